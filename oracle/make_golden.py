@@ -1,0 +1,188 @@
+"""Oracle (test infrastructure): generates tests/golden/*.npz by running the REAL
+reference code (/root/reference, build container only) on the reference's own
+fixtures and on adversarial inputs.  Re-run with
+
+    python -m oracle.make_golden
+
+The reference has no tests or golden vectors of its own,
+so these files ARE the pin: ``tests/test_oracle_golden.py`` checks the CPU
+restatement in ``oracle/`` against them, and the ``-m gpu`` tests check the CUDA
+path against them and against the oracle.
+"""
+import hashlib
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import ref_harness  # noqa: E402
+from eventgpt_b200.weights import random_state_dict  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+REF = ref_harness.REF
+N_FRAMES = 5
+
+
+def load_npy(path):
+    return np.array(np.load(path, allow_pickle=True)).item()
+
+
+def adversarial_cases():
+    rng = np.random.default_rng(1234)
+    cases = {}
+    # every event on one pixel, alternating polarity: order sensitivity
+    n = 1003
+    cases["adv_one_pixel"] = dict(x=np.full(n, 7, np.uint16), y=np.full(n, 3, np.uint16),
+                                  t=np.arange(n, dtype=np.int64), p=(np.arange(n) % 2).astype(np.uint8))
+    # remainder handling (common/common.py:27): 5, 6, 7, 9 events
+    for n in (5, 6, 7, 9):
+        cases[f"adv_n{n}"] = dict(x=rng.integers(0, 20, n).astype(np.uint16), y=rng.integers(0, 12, n).astype(np.uint16),
+                                  t=np.sort(rng.integers(0, 50000, n)).astype(np.int64), p=rng.integers(0, 2, n).astype(np.uint8))
+    # p in {-1,+1}: -1 is painted red (common/common.py:69-72)
+    n = 4001
+    cases["adv_signed_p"] = dict(x=rng.integers(0, 64, n).astype(np.int64), y=rng.integers(0, 48, n).astype(np.int64),
+                                 t=np.sort(rng.integers(0, 50000, n)).astype(np.int64),
+                                 p=(rng.integers(0, 2, n) * 2 - 1).astype(np.int64))
+    # p in {0,1,2,255}: any non-zero is red
+    cases["adv_p_multi"] = dict(x=rng.integers(0, 90, n).astype(np.uint16), y=rng.integers(0, 70, n).astype(np.uint16),
+                                t=np.sort(rng.integers(0, 50000, n)).astype(np.uint16),
+                                p=rng.choice(np.array([0, 1, 2, 255], np.uint8), n))
+    # hot pixels (Zipf) on a VGA sensor: heavy collisions
+    n = 60000
+    z = np.minimum(rng.zipf(1.3, n) - 1, 640 * 480 - 1)
+    perm = rng.permutation(640 * 480)
+    lin = perm[z]
+    cases["adv_zipf_vga"] = dict(x=(lin % 640).astype(np.uint16), y=(lin // 640).astype(np.uint16),
+                                 t=np.sort(rng.integers(0, 50000, n)).astype(np.int64), p=rng.integers(0, 2, n).astype(np.uint8))
+    # tall sensor (H > W): resize takes the other branch
+    n = 30000
+    cases["adv_tall"] = dict(x=rng.integers(0, 260, n).astype(np.uint16), y=rng.integers(0, 346, n).astype(np.uint16),
+                             t=np.sort(rng.integers(0, 50000, n)).astype(np.int64), p=rng.integers(0, 2, n).astype(np.uint8))
+    # Gen4-class 1280x720
+    n = 150000
+    cases["adv_720p"] = dict(x=rng.integers(0, 1280, n).astype(np.uint16), y=rng.integers(0, 720, n).astype(np.uint16),
+                             t=np.sort(rng.integers(0, 50000, n)).astype(np.int64), p=rng.integers(0, 2, n).astype(np.uint8))
+    # square, exactly 336 (no resize pass at all) and an upscale case
+    n = 20000
+    cases["adv_336sq"] = dict(x=rng.integers(0, 336, n).astype(np.uint16), y=rng.integers(0, 336, n).astype(np.uint16),
+                              t=np.sort(rng.integers(0, 50000, n)).astype(np.int64), p=rng.integers(0, 2, n).astype(np.uint8))
+    n = 3000
+    cases["adv_small_up"] = dict(x=rng.integers(0, 120, n).astype(np.uint16), y=rng.integers(0, 100, n).astype(np.uint16),
+                                 t=np.sort(rng.integers(0, 50000, n)).astype(np.int64), p=rng.integers(0, 2, n).astype(np.uint8))
+    return cases
+
+
+def reference_cases():
+    cases = {"sample1": load_npy(f"{REF}/samples/sample1.npy")}
+    d = f"{REF}/feasible/egpt_dataset/event_npy/interlaken_00_d"
+    for f in ("000069", "000099"):
+        cases[f"dsec_{f}"] = load_npy(f"{d}/{f}.npy")
+    d = f"{REF}/feasible/my_egpt_dsec_dataset/example_event_npy"
+    for i in range(10):
+        cases[f"synthetic_{i:06d}"] = load_npy(f"{d}/synthetic_{i:06d}.npy")
+    return cases
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    C, M = ref_harness.import_reference()
+    proc = ref_harness.pil_processor()
+    cases = reference_cases()
+    cases.update(adversarial_cases())
+    manifest = []
+    for name, ev in cases.items():
+        ev = {k: np.asarray(ev[k]) for k in ("x", "y", "t", "p")}
+        frames = C.get_event_images_list(ev, N_FRAMES)                      # common/common.py:17-37
+        hw = np.array([f.shape[:2] for f in frames], np.int32)
+        pix = []
+        for f in frames:                                                    # common/common.py:124-127
+            pv = proc(f, return_tensors="pt")["pixel_values"][0]
+            pix.append(pv.to(torch.bfloat16).view(torch.int16).numpy().view(np.uint16))
+        pix = np.stack(pix)
+        packed = np.concatenate([f.reshape(-1) for f in frames])
+        np.savez_compressed(os.path.join(OUT, f"events_{name}.npz"), x=ev["x"], y=ev["y"], t=ev["t"], p=ev["p"],
+                            frame_hw=hw, frames=packed, pix=pix)
+        manifest.append((name, len(ev["t"]), hw.tolist(), hashlib.sha256(pix.tobytes()).hexdigest()[:16]))
+        print(name, len(ev["t"]), hw.tolist())
+
+    # uint8 level -> bf16 LUT straight from the processor
+    ramp = np.zeros((336, 336, 3), np.uint8)
+    ramp[:] = (np.arange(336) % 256).astype(np.uint8)[None, :, None]
+    pv = proc(ramp, return_tensors="pt")["pixel_values"][0]                 # [3,336,336]
+    lut_f32 = pv[:, 0, :256].T.contiguous().numpy()                        # [256,3]
+    lut_bf16 = pv[:, 0, :256].T.contiguous().to(torch.bfloat16).view(torch.int16).numpy().view(np.uint16)
+    np.savez_compressed(os.path.join(OUT, "normalise_lut.npz"), f32=lut_f32, bf16=lut_bf16)
+
+    # process_event_data end to end on the reference's own sample (common/common.py:110-129)
+    size, evl = C.process_event_data(f"{REF}/samples/sample1.npy", proc, "cpu")
+    ped = torch.stack(evl).view(torch.int16).numpy().view(np.uint16)
+    ref_pix = np.load(os.path.join(OUT, "events_sample1.npz"))["pix"]
+    assert np.array_equal(ped, ref_pix) and size == [480, 640]
+
+    # split_event_by_time (common/common.py:76-107): unsorted t, gaps (empty bins), 3 dtypes
+    rng = np.random.default_rng(77)
+    n = 50000
+    t = rng.integers(0, 400000, n).astype(np.int64)
+    t[(t >= 100000) & (t < 200000)] += 200000            # leave bins 100000, 150000 empty
+    half = n // 2
+    t[:half] = np.sort(t[:half])                          # half sorted, half not
+    stream = dict(x=rng.integers(0, 640, n).astype(np.uint16), y=rng.integers(0, 480, n).astype(np.uint16),
+                  t=t, p=rng.integers(0, 2, n).astype(np.uint8))
+    parts = C.split_event_by_time(stream, 50000)
+    np.savez_compressed(os.path.join(OUT, "split_stream.npz"), **stream,
+                        counts=np.array([len(q["t"]) for q in parts], np.int64),
+                        out_x=np.concatenate([q["x"] for q in parts]), out_y=np.concatenate([q["y"] for q in parts]),
+                        out_t=np.concatenate([q["t"] for q in parts]), out_p=np.concatenate([q["p"] for q in parts]))
+    print("split bins", [len(q["t"]) for q in parts])
+
+    # tower -> projector -> adaptor -> pooling through the reference's list branch
+    # (model/EventChatModel.py:326-343), fp32 CPU, seeded weights.
+    evl32 = [e.float() for e in evl]
+    for layers in (2, 24):
+        sd = random_state_dict(seed=0, num_layers=layers)
+        C2, M2, model = ref_harness.build_reference_model(sd, num_layers=layers)
+        with torch.no_grad():
+            # visval_encode = tower.last_hidden_state -> projector (:194-200)
+            f0 = model.visval_encode(evl32[0][None]).detach()
+            lhs0 = model.get_model().visual_tower.visual_tower(evl32[0][None]).last_hidden_state
+            feats = []
+            for ev in evl32:
+                f = model.visval_encode(ev[None]).detach()
+                f = model.get_model().feature_adaptor(f)[0]
+                feats.append(f)
+            tokens = M2.get_spatio_temporal_features(feats)                 # [582,4096]
+            # and once through prepare_inputs_labels_for_multimodal itself
+            ids = torch.tensor([[1, -200, 5, 6]])
+            out = model.prepare_inputs_labels_for_multimodal(ids, None, None, None, None, event_tensors=evl32)
+            embeds = out[4]
+            assert embeds.shape == (1, 585, 4096)
+            assert torch.equal(embeds[0, 1:583], tokens)
+        wsum = float(sum(v.double().abs().sum() for v in sd.values()))
+        np.savez_compressed(os.path.join(OUT, f"tokens_sample1_L{layers}.npz"),
+                            tokens_sub=tokens[:, ::16].numpy(), tokens_rows=tokens[[0, 4, 5, 300, 581]].numpy(),
+                            lhs0_sub=lhs0[0, :, ::8].numpy(), proj0_sub=f0[0, :, ::16].numpy(),
+                            absmax=np.float32(tokens.abs().max()), std=np.float32(tokens.std()),
+                            weight_abs_sum=np.float64(wsum))
+        print("tokens L", layers, tokens.shape, float(tokens.abs().max()), float(tokens.std()), wsum)
+        # yardstick: the reference's own bf16 execution vs its fp32
+        if layers == 24:
+            mb = model.to(torch.bfloat16)
+            with torch.no_grad():
+                fb = []
+                for ev in evl:
+                    f = mb.visval_encode(ev[None]).detach()
+                    fb.append(mb.get_model().feature_adaptor(f)[0])
+                tb = M2.get_spatio_temporal_features(fb).float()
+            d = (tb - tokens).abs().max().item()
+            cos = torch.nn.functional.cosine_similarity(tb.flatten(), tokens.flatten(), dim=0).item()
+            print("torch-bf16 vs fp32: max-abs", d, "cos", cos)
+            np.savez(os.path.join(OUT, "yardstick_bf16.npz"), max_abs=np.float32(d), cosine=np.float32(cos))
+    for m in manifest:
+        print(m)
+
+
+if __name__ == "__main__":
+    main()
