@@ -1,0 +1,261 @@
+// Persistent warp-specialised bf16 GEMM for sm_100a:  C = epilogue(A[M,K] . B[N,K]^T + bias)
+//
+// Used for every linear layer of the visual-token stage (reference:
+// transformers modeling_clip.py CLIPAttention / CLIPMLP called from
+// model/EventChatModel.py:196, visual_projector :96-102,199 and feature_adaptor
+// :84-85,338).  nn.Linear stores weight as [out, in] = [N, K] K-major, which is
+// exactly the B operand layout tcgen05 wants, so weights are used as they are.
+//
+// Structure (one CTA per SM, 256 threads):
+//   warp 0    TMA producer: A (128 x 64) and B (256 x 64) bf16 tiles, SWIZZLE_128B,
+//             4-stage mbarrier ring
+//   warp 1    MMA issuer: one thread issues tcgen05.mma (M128 N256 K16), fp32
+//             accumulators in TMEM, double-buffered (2 x 256 columns)
+//   warp 2    TMEM allocator
+//   warps 4-7 epilogue: tcgen05.ld 32 lanes x 32 columns -> bias / activation /
+//             fp32 residual add -> global
+// Tiles are walked n-fastest so the CTAs running concurrently share A rows through L2.
+#include "common.cuh"
+#include "sm100_ptx.cuh"
+#include <mutex>
+
+namespace egpt {
+
+constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16;
+constexpr int kStages = 4;
+constexpr int kABytes = BM * BK * 2;               // 16 KB
+constexpr int kBBytes = BN * BK * 2;               // 32 KB
+constexpr int kStageBytes = kABytes + kBBytes;     // 48 KB
+constexpr int kTmemCols = 2 * BN;                  // two accumulator stages
+constexpr int kGemmThreads = 256;
+constexpr int kGemmSmem = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+
+enum { EPI_BIAS_BF16 = 0, EPI_QUICKGELU_BF16 = 1, EPI_GELU_BF16 = 2, EPI_RESIDUAL_F32 = 3, EPI_STORE_F32 = 4 };
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+template <int EPI>
+__device__ __forceinline__ float activate(float v) {
+  if (EPI == EPI_QUICKGELU_BF16) return v / (1.0f + __expf(-1.702f * v));        // x * sigmoid(1.702 x)
+  if (EPI == EPI_GELU_BF16) return 0.5f * v * (1.0f + erff(v * 0.70710678118654752f));
+  return v;
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const float* __restrict__ bias, void* __restrict__ out, long long M, int N, int K) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full = empty_bar + kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tiles = N / BN;
+  const long long m_tiles = (M + BM - 1) / BM;
+  const long long num_tiles = m_tiles * n_tiles;
+  const int num_kb = K / BK;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tensormap(&tmap_a);
+    ptx::prefetch_tensormap(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kStages; ++i) { ptx::mbar_init(full_bar + i, 1); ptx::mbar_init(empty_bar + i, 1); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(tmem_full + i, 1); ptx::mbar_init(tmem_empty + i, 128); }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) {
+    ptx::tmem_alloc(tmem_ptr, kTmemCols);
+    ptx::tmem_relinquish();
+  }
+  ptx::tcgen05_fence_before();
+  __syncthreads();
+  ptx::tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0 && lane == 0) {
+    // ===== TMA producer =====
+    int stage = 0; uint32_t phase = 0;
+    for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m0 = (int)(tile / n_tiles) * BM, n0 = (int)(tile % n_tiles) * BN;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        ptx::mbar_wait(empty_bar + stage, phase ^ 1);
+        uint8_t* sa = smem + stage * kStageBytes;
+        ptx::mbar_arrive_expect_tx(full_bar + stage, kStageBytes);
+        ptx::tma_load_2d(sa, &tmap_a, full_bar + stage, kb * BK, m0);
+        ptx::tma_load_2d(sa + kABytes, &tmap_b, full_bar + stage, kb * BK, n0);
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ===== MMA issuer =====
+    constexpr uint32_t idesc = ptx::make_idesc_bf16(BM, BN);
+    int stage = 0; uint32_t phase = 0;
+    int acc = 0; uint32_t acc_phase = 0;
+    for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      ptx::mbar_wait(tmem_empty + acc, acc_phase ^ 1);
+      ptx::tcgen05_fence_after();
+      const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        ptx::mbar_wait(full_bar + stage, phase);
+        ptx::tcgen05_fence_after();
+        const uint32_t sa = ptx::smem_u32(smem + stage * kStageBytes);
+        const uint64_t da = ptx::make_smem_desc_sw128(sa), db = ptx::make_smem_desc_sw128(sa + kABytes);
+#pragma unroll
+        for (int k = 0; k < BK / UMMA_K; ++k) {
+          // advance 32 B (16 bf16) inside the 128 B swizzle atom: +2 in 16-byte units
+          ptx::umma_bf16_ss(tmem_d, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+        }
+        ptx::umma_commit(empty_bar + stage);          // smem slot free once these MMAs retire
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
+      }
+      ptx::umma_commit(tmem_full + acc);              // accumulator ready for the epilogue
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue =====
+    const int q = warp & 3;                            // TMEM lane quadrant this warp may read
+    int acc = 0; uint32_t acc_phase = 0;
+    for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const long long row = (tile / n_tiles) * BM + q * 32 + lane;
+      const int n0 = (int)(tile % n_tiles) * BN;
+      ptx::mbar_wait(tmem_full + acc, acc_phase);
+      ptx::tcgen05_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, r);
+        ptx::tmem_ld_wait();
+        if (row < M) {
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          if (bias != nullptr) {
+            const float4* bp = reinterpret_cast<const float4*>(bias + n0 + c0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 b = __ldg(bp + j);
+              v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+            }
+          }
+          if (EPI == EPI_RESIDUAL_F32 || EPI == EPI_STORE_F32) {
+            float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + row * N + n0 + c0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float4 o = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+              if (EPI == EPI_RESIDUAL_F32) {
+                const float4 h = op[j];
+                o.x += h.x; o.y += h.y; o.z += h.z; o.w += h.w;
+              }
+              op[j] = o;
+            }
+          } else {
+            uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(out) + row * N + n0 + c0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 o;
+              o.x = pack_bf16(activate<EPI>(v[8 * j + 0]), activate<EPI>(v[8 * j + 1]));
+              o.y = pack_bf16(activate<EPI>(v[8 * j + 2]), activate<EPI>(v[8 * j + 3]));
+              o.z = pack_bf16(activate<EPI>(v[8 * j + 4]), activate<EPI>(v[8 * j + 5]));
+              o.w = pack_bf16(activate<EPI>(v[8 * j + 6]), activate<EPI>(v[8 * j + 7]));
+              op[j] = o;
+            }
+          }
+        }
+      }
+      ptx::tcgen05_fence_before();
+      ptx::mbar_arrive(tmem_empty + acc);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  ptx::tcgen05_fence_before();
+  __syncthreads();
+  ptx::tcgen05_fence_after();
+  if (warp == 2) ptx::tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ---- host side -----------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// 2-D bf16 row-major [rows, cols] tensor, box = {BK columns, box_rows rows}, 128-byte swizzle
+int make_tmap_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) { set_error("cuTensorMapEncodeTiled entry point not available"); return EGPT_ERR_CUDA; }
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {cols * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return EGPT_ERR_CUDA; }
+  return EGPT_OK;
+}
+
+template <int EPI>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const float* bias, void* out, long long M, int N,
+                       int K, cudaStream_t stream) {
+  static std::once_flag once;   // attribute is per function; one process drives one device
+  cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(gemm_bf16_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem);
+  });
+  EGPT_CUDA(attr_err);
+  const long long tiles = ((M + BM - 1) / BM) * (N / BN);
+  const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
+  gemm_bf16_kernel<EPI><<<grid, kGemmThreads, kGemmSmem, stream>>>(ta, tb, bias, out, M, N, K);
+  EGPT_LAUNCH_CHECK();
+  return EGPT_OK;
+}
+
+int gemm_bf16(const void* A, const void* B, const float* bias, void* out, long long M, int N, int K, int epilogue,
+              cudaStream_t stream) {
+  EGPT_CHECK_ARG(A && B && out, "gemm: null pointer");
+  EGPT_CHECK_ARG(M > 0 && N > 0 && K > 0 && N % BN == 0 && K % BK == 0, "gemm: unsupported shape M=%lld N=%d K=%d (N %% 256, K %% 64)",
+                 M, N, K);
+  EGPT_CHECK_ARG(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
+                 (bias == nullptr || (uintptr_t)bias % 16 == 0), "gemm: pointers must be 16-byte aligned");
+  CUtensorMap ta, tb;
+  EGPT_TRY(make_tmap_bf16(&ta, A, (uint64_t)M, (uint64_t)K, BM));
+  EGPT_TRY(make_tmap_bf16(&tb, B, (uint64_t)N, (uint64_t)K, BN));
+  switch (epilogue) {
+    case EPI_BIAS_BF16: return launch_gemm<EPI_BIAS_BF16>(ta, tb, bias, out, M, N, K, stream);
+    case EPI_QUICKGELU_BF16: return launch_gemm<EPI_QUICKGELU_BF16>(ta, tb, bias, out, M, N, K, stream);
+    case EPI_GELU_BF16: return launch_gemm<EPI_GELU_BF16>(ta, tb, bias, out, M, N, K, stream);
+    case EPI_RESIDUAL_F32: return launch_gemm<EPI_RESIDUAL_F32>(ta, tb, bias, out, M, N, K, stream);
+    case EPI_STORE_F32: return launch_gemm<EPI_STORE_F32>(ta, tb, bias, out, M, N, K, stream);
+  }
+  set_error("gemm: unknown epilogue %d", epilogue);
+  return EGPT_ERR_INVALID;
+}
+
+}  // namespace egpt
+
+extern "C" int egpt_gemm_bf16(const uint16_t* A, const uint16_t* B, const float* bias, void* out, int64_t M, int N,
+                              int K, int epilogue, void* stream) {
+  return egpt::gemm_bf16(A, B, bias, out, M, N, K, epilogue, (cudaStream_t)stream);
+}

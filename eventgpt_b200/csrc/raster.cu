@@ -1,0 +1,494 @@
+// Event-stream splitting and order-exact rasterisation (sm_100a).
+//
+// Replaces, bit for bit, common/common.py:17-37 (get_event_images_list),
+// :64-74 (generate_event_image) and :76-107 (split_event_by_time) of the
+// reference, plus the "negative wins" raster of
+// feasible/my_egpt_dsec_dataset/preprocess_event_images.py:58-90.
+//
+// Rasterisation is "last event at a pixel wins", which is not commutative.  It
+// is made order-free with a key  ((index_in_slice + 1) << 1) | (p != 0)  and an
+// atomicMax into a per-frame uint32 key plane; a second kernel turns keys into
+// RGB.  Key planes are scratch: they are processed in chunks of windows small
+// enough to stay resident in the 126 MB L2, so DRAM traffic stays at the
+// algorithmic 5 B/event read + 3 B/pixel written.
+#include "common.cuh"
+
+namespace egpt {
+
+constexpr int kScatterThreads = 256;
+constexpr size_t kKeyPlaneL2Budget = 48u << 20;   // bytes of key planes kept live per chunk
+
+struct SliceInfo {
+  long long start, end;
+};
+
+// slice i of a window [s, e): k = (e-s)/n, [s+i*k, s+(i+1)*k), last slice takes the remainder
+__device__ __forceinline__ SliceInfo slice_bounds(const int64_t* __restrict__ offsets, int window, int i, int n) {
+  long long s = offsets[window], e = offsets[window + 1];
+  long long k = (e - s) / n;
+  SliceInfo r;
+  r.start = s + (long long)i * k;
+  r.end = (i < n - 1) ? s + (long long)(i + 1) * k : e;
+  return r;
+}
+
+__device__ __forceinline__ void emit_event(unsigned x, unsigned y, unsigned pz, unsigned key_last, int mode,
+                                           int H, int W, uint32_t* __restrict__ plane, int32_t* __restrict__ counts,
+                                           unsigned& mx, unsigned& my, unsigned& flags) {
+  if (x >= (unsigned)W || y >= (unsigned)H) { flags |= EGPT_FLAG_OUT_OF_RANGE; return; }
+  mx = max(mx, x);
+  my = max(my, y);
+  unsigned pix = y * (unsigned)W + x;
+  if (mode == EGPT_RASTER_LAST_WINS) {
+    atomicMax(plane + pix, key_last | (pz ? 0u : 1u));
+    if (counts) atomicAdd(counts + (size_t)(pz ? 0 : 1) * H * W + pix, 1);
+  }
+}
+
+// One CTA column per slice (blockIdx.y); CTAs of a column stride over the slice.
+// FAST: x,y uint16 and p uint8 with 16/16/8-byte aligned bases -> 128-bit loads of 8 events.
+template <bool FAST>
+__global__ void __launch_bounds__(kScatterThreads)
+raster_scatter_kernel(const void* __restrict__ xv, const void* __restrict__ yv, const void* __restrict__ pv,
+                      int xdt, int ydt, int pdt, const int64_t* __restrict__ offsets,
+                      int window0, int n_frames, int mode, int H, int W, int fixed_canvas,
+                      uint32_t* __restrict__ planes, int32_t* __restrict__ out_hw,
+                      int32_t* __restrict__ out_counts, int32_t* __restrict__ status) {
+  const int local_slice = blockIdx.y;
+  const int window = window0 + local_slice / n_frames;
+  const int fi = local_slice % n_frames;
+  const int frame = window * n_frames + fi;
+  const SliceInfo sl = slice_bounds(offsets, window, fi, n_frames);
+  uint32_t* plane = planes + (size_t)local_slice * H * W;
+  int32_t* counts = out_counts ? out_counts + (size_t)frame * 2 * H * W : nullptr;
+  unsigned mx = 0, my = 0, flags = 0;
+  bool any = false;
+
+  if (sl.end <= sl.start) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(status, EGPT_FLAG_EMPTY_SLICE);
+    return;
+  }
+
+  if (FAST) {
+    const long long g0 = sl.start >> 3, g1 = (sl.end + 7) >> 3;   // groups of 8 events
+    for (long long g = g0 + (long long)blockIdx.x * kScatterThreads + threadIdx.x; g < g1;
+         g += (long long)gridDim.x * kScatterThreads) {
+      const long long base = g << 3;
+      unsigned xw[4], yw[4], pw[2];
+      if (base >= sl.start && base + 8 <= sl.end) {
+        const uint4 xs = __ldg(reinterpret_cast<const uint4*>(xv) + g);
+        const uint4 ys = __ldg(reinterpret_cast<const uint4*>(yv) + g);
+        const uint2 ps = __ldg(reinterpret_cast<const uint2*>(pv) + g);
+        xw[0] = xs.x; xw[1] = xs.y; xw[2] = xs.z; xw[3] = xs.w;
+        yw[0] = ys.x; yw[1] = ys.y; yw[2] = ys.z; yw[3] = ys.w;
+        pw[0] = ps.x; pw[1] = ps.y;
+      } else {
+        // boundary group: element loads, never outside [start, end)
+        xw[0] = xw[1] = xw[2] = xw[3] = yw[0] = yw[1] = yw[2] = yw[3] = pw[0] = pw[1] = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const long long i = base + j;
+          if (i < sl.start || i >= sl.end) continue;
+          xw[j >> 1] |= (unsigned)((const uint16_t*)xv)[i] << ((j & 1) * 16);
+          yw[j >> 1] |= (unsigned)((const uint16_t*)yv)[i] << ((j & 1) * 16);
+          pw[j >> 2] |= (unsigned)((const uint8_t*)pv)[i] << ((j & 3) * 8);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const long long i = base + j;
+        if (i < sl.start || i >= sl.end) continue;
+        const unsigned x = (xw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
+        const unsigned y = (yw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
+        const unsigned p = (pw[j >> 2] >> ((j & 3) * 8)) & 0xffu;
+        any = true;
+        if (mode == EGPT_RASTER_LAST_WINS) {
+          emit_event(x, y, p == 0, (unsigned)(i - sl.start + 1) << 1, mode, H, W, plane, counts, mx, my, flags);
+        } else {
+          if (x >= (unsigned)W || y >= (unsigned)H) { flags |= EGPT_FLAG_OUT_OF_RANGE; continue; }
+          mx = max(mx, x); my = max(my, y);
+          if (p == 0) atomicMax(plane + y * (unsigned)W + x, 2u);
+          else if (p == 1) atomicMax(plane + y * (unsigned)W + x, 1u);
+        }
+      }
+    }
+  } else {
+    for (long long i = sl.start + (long long)blockIdx.x * kScatterThreads + threadIdx.x; i < sl.end;
+         i += (long long)gridDim.x * kScatterThreads) {
+      const long long xl = load_int(xv, xdt, i), yl = load_int(yv, ydt, i), pl = load_int(pv, pdt, i);
+      any = true;
+      if (xl < 0 || yl < 0 || xl >= W || yl >= H) { flags |= EGPT_FLAG_OUT_OF_RANGE; continue; }
+      const unsigned x = (unsigned)xl, y = (unsigned)yl;
+      if (mode == EGPT_RASTER_LAST_WINS) {
+        emit_event(x, y, pl == 0, (unsigned)(i - sl.start + 1) << 1, mode, H, W, plane, counts, mx, my, flags);
+      } else {
+        mx = max(mx, x); my = max(my, y);
+        if (pl == 0) atomicMax(plane + y * (unsigned)W + x, 2u);
+        else if (pl == 1) atomicMax(plane + y * (unsigned)W + x, 1u);
+      }
+    }
+  }
+
+  // canvas extent = (max y + 1, max x + 1) of the slice (common/common.py:65)
+  if (!fixed_canvas) {
+    unsigned vx = any ? mx + 1 : 0, vy = any ? my + 1 : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      vx = max(vx, __shfl_xor_sync(0xffffffffu, vx, o));
+      vy = max(vy, __shfl_xor_sync(0xffffffffu, vy, o));
+    }
+    if ((threadIdx.x & 31) == 0 && vx) {
+      atomicMax(out_hw + 2 * frame + 0, (int)vy);
+      atomicMax(out_hw + 2 * frame + 1, (int)vx);
+    }
+  }
+  flags = __reduce_or_sync(0xffffffffu, flags);
+  if ((threadIdx.x & 31) == 0 && flags) atomicOr(status, (int)flags);
+}
+
+__global__ void set_fixed_hw_kernel(int32_t* __restrict__ hw, int n, int H, int W) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) { hw[2 * i] = H; hw[2 * i + 1] = W; }
+}
+
+__device__ __forceinline__ unsigned rgb_of_key(unsigned key) {
+  // little-endian byte triple: white 255,255,255; red 255,0,0 (odd key); blue 0,0,255
+  return key == 0 ? 0x00ffffffu : ((key & 1u) ? 0x000000ffu : 0x00ff0000u);
+}
+
+// keys -> packed RGB; 16 pixels (64 B of keys -> 48 B of RGB) per thread.
+__global__ void __launch_bounds__(256)
+raster_colourise_kernel(const uint32_t* __restrict__ planes, const int32_t* __restrict__ out_hw,
+                        int frame0, int H, int W, uint8_t* __restrict__ out_frames, size_t frame_stride) {
+  const int local = blockIdx.y;
+  const int frame = frame0 + local;
+  const int h = out_hw[2 * frame], w = out_hw[2 * frame + 1];
+  const long long npix = (long long)h * w;
+  if (npix == 0) return;
+  const uint32_t* plane = planes + (size_t)local * H * W;
+  uint8_t* dst = out_frames + (size_t)frame * frame_stride;
+  const long long ngroups = (npix + 15) >> 4;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < ngroups;
+       g += (long long)gridDim.x * blockDim.x) {
+    const long long p0 = g << 4;
+    unsigned c[16];
+    if (w == W && p0 + 16 <= npix && ((reinterpret_cast<uintptr_t>(plane + p0) & 15) == 0)) {
+      const uint4* kp = reinterpret_cast<const uint4*>(plane + p0);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint4 k = kp[q];
+        c[4 * q + 0] = rgb_of_key(k.x); c[4 * q + 1] = rgb_of_key(k.y);
+        c[4 * q + 2] = rgb_of_key(k.z); c[4 * q + 3] = rgb_of_key(k.w);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const long long p = p0 + j;
+        unsigned key = 0;
+        if (p < npix) {
+          const int yy = (int)(p / w), xx = (int)(p - (long long)yy * w);
+          key = plane[(size_t)yy * W + xx];
+        }
+        c[j] = rgb_of_key(key);
+      }
+    }
+    if (p0 + 16 <= npix) {
+      // 4 pixels (12 B) -> 3 words; 16 pixels -> 12 words -> 3 x uint4
+      unsigned wds[12];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const unsigned a = c[4 * q], b = c[4 * q + 1], d = c[4 * q + 2], e = c[4 * q + 3];
+        wds[3 * q + 0] = a | (b << 24);
+        wds[3 * q + 1] = (b >> 8) | (d << 16);
+        wds[3 * q + 2] = (d >> 16) | (e << 8);
+      }
+      uint4* o = reinterpret_cast<uint4*>(dst + p0 * 3);
+      o[0] = make_uint4(wds[0], wds[1], wds[2], wds[3]);
+      o[1] = make_uint4(wds[4], wds[5], wds[6], wds[7]);
+      o[2] = make_uint4(wds[8], wds[9], wds[10], wds[11]);
+    } else {
+      for (int j = 0; j < 16 && p0 + j < npix; ++j) {
+        uint8_t* o = dst + (p0 + j) * 3;
+        o[0] = c[j] & 0xff; o[1] = (c[j] >> 8) & 0xff; o[2] = (c[j] >> 16) & 0xff;
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// split_event_by_time: stable counting sort of events by time bin.
+// ------------------------------------------------------------------------------------------
+constexpr int kSplitMaxChunks = 4096;
+
+__device__ __forceinline__ long long floor_div(long long a, long long b) {
+  long long q = a / b;
+  if ((a % b != 0) && ((a < 0) != (b < 0))) --q;
+  return q;
+}
+
+struct SplitPlan {
+  long long n;
+  long long chunk;     // events per chunk (multiple of 32)
+  int n_chunks;
+  int span_cap;        // capacity of the dense bin table (= max_windows)
+};
+
+__global__ void split_minmax_kernel(const void* __restrict__ t, int tdt, long long n, long long interval,
+                                    long long* __restrict__ minmax) {
+  long long lo = 0x7fffffffffffffffLL, hi = -0x7fffffffffffffffLL - 1;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    long long b = floor_div(load_int(t, tdt, i), interval);
+    lo = min(lo, b); hi = max(hi, b);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  if ((threadIdx.x & 31) == 0) { atomicMin(minmax, lo); atomicMax(minmax + 1, hi); }
+}
+
+__global__ void split_init_kernel(long long* minmax) {
+  minmax[0] = 0x7fffffffffffffffLL;
+  minmax[1] = -0x7fffffffffffffffLL - 1;
+}
+
+// one warp per chunk
+__global__ void split_count_kernel(const void* __restrict__ t, int tdt, SplitPlan plan, long long interval,
+                                   const long long* __restrict__ minmax, int32_t* __restrict__ table,
+                                   int32_t* __restrict__ status) {
+  const int chunk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (chunk >= plan.n_chunks) return;
+  const long long lo = minmax[0], span = minmax[1] - lo + 1;
+  if (span > plan.span_cap) { if (lane == 0 && chunk == 0) atomicOr(status, EGPT_FLAG_TOO_MANY_BINS); return; }
+  const long long s = (long long)chunk * plan.chunk, e = min(plan.n, s + plan.chunk);
+  int32_t* row = table + (size_t)chunk * plan.span_cap;
+  for (long long b0 = s; b0 < e; b0 += 32) {
+    const long long i = b0 + lane;
+    const int rb = i < e ? (int)(floor_div(load_int(t, tdt, i), interval) - lo) : -1;
+    const unsigned m = __match_any_sync(0xffffffffu, rb);
+    if (rb >= 0 && lane == __ffs(m) - 1) row[rb] += __popc(m);
+    __syncwarp();
+  }
+}
+
+// single CTA: per-bin totals, compaction of non-empty bins into window offsets, then
+// per-(chunk,bin) destination offsets written back into the table.
+__global__ void __launch_bounds__(1024)
+split_scan_kernel(SplitPlan plan, const long long* __restrict__ minmax, int32_t* __restrict__ table,
+                  long long* __restrict__ bin_start, int64_t* __restrict__ out_offsets,
+                  int32_t* __restrict__ out_nwindows, int max_windows) {
+  const long long span = minmax[1] - minmax[0] + 1;
+  if (span > plan.span_cap) { if (threadIdx.x == 0) { *out_nwindows = 0; out_offsets[0] = 0; } return; }
+  for (int rb = threadIdx.x; rb < span; rb += blockDim.x) {
+    long long tot = 0;
+    for (int c = 0; c < plan.n_chunks; ++c) tot += table[(size_t)c * plan.span_cap + rb];
+    bin_start[rb] = tot;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long run = 0; int nw = 0;
+    out_offsets[0] = 0;
+    for (int rb = 0; rb < span; ++rb) {
+      const long long c = bin_start[rb];
+      bin_start[rb] = run;
+      run += c;
+      if (c > 0) { ++nw; if (nw <= max_windows) out_offsets[nw] = run; }
+    }
+    *out_nwindows = nw;
+  }
+  __syncthreads();
+  for (int rb = threadIdx.x; rb < span; rb += blockDim.x) {
+    long long run = bin_start[rb];
+    for (int c = 0; c < plan.n_chunks; ++c) {
+      int32_t* cell = table + (size_t)c * plan.span_cap + rb;
+      const int32_t cnt = *cell;
+      // destinations are < 2^31 per chunk row only when n < 2^31; larger streams are rejected on the host
+      *cell = (int32_t)run;
+      run += cnt;
+    }
+  }
+}
+
+__device__ __forceinline__ void copy_elem(void* __restrict__ dst, const void* __restrict__ src, int size,
+                                          long long d, long long s) {
+  switch (size) {
+    case 1: ((uint8_t*)dst)[d] = ((const uint8_t*)src)[s]; break;
+    case 2: ((uint16_t*)dst)[d] = ((const uint16_t*)src)[s]; break;
+    case 4: ((uint32_t*)dst)[d] = ((const uint32_t*)src)[s]; break;
+    default: ((uint64_t*)dst)[d] = ((const uint64_t*)src)[s]; break;
+  }
+}
+
+__global__ void split_scatter_kernel(const void* __restrict__ x, const void* __restrict__ y,
+                                     const void* __restrict__ t, const void* __restrict__ p,
+                                     int xs, int ys, int tdt, int ps, SplitPlan plan, long long interval,
+                                     const long long* __restrict__ minmax, int32_t* __restrict__ table,
+                                     void* __restrict__ ox, void* __restrict__ oy, void* __restrict__ ot,
+                                     void* __restrict__ op) {
+  const int chunk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (chunk >= plan.n_chunks) return;
+  const long long lo = minmax[0], span = minmax[1] - lo + 1;
+  if (span > plan.span_cap) return;
+  const long long s = (long long)chunk * plan.chunk, e = min(plan.n, s + plan.chunk);
+  int32_t* row = table + (size_t)chunk * plan.span_cap;
+  const int ts = dtype_size(tdt);
+  for (long long b0 = s; b0 < e; b0 += 32) {
+    const long long i = b0 + lane;
+    const int rb = i < e ? (int)(floor_div(load_int(t, tdt, i), interval) - lo) : -1;
+    const unsigned m = __match_any_sync(0xffffffffu, rb);
+    const int leader = __ffs(m) - 1;
+    int base = 0;
+    if (rb >= 0 && lane == leader) { base = row[rb]; row[rb] = base + __popc(m); }
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (rb >= 0) {
+      const long long d = (long long)base + __popc(m & ((1u << lane) - 1u));
+      copy_elem(ox, x, xs, d, i);
+      copy_elem(oy, y, ys, d, i);
+      copy_elem(ot, t, ts, d, i);
+      copy_elem(op, p, ps, d, i);
+    }
+    __syncwarp();
+  }
+}
+
+static SplitPlan make_split_plan(long long n, int max_windows) {
+  SplitPlan pl;
+  pl.n = n;
+  long long chunks = (n + 1023) / 1024;
+  if (chunks > kSplitMaxChunks) chunks = kSplitMaxChunks;
+  if (chunks < 1) chunks = 1;
+  long long chunk = (n + chunks - 1) / chunks;
+  chunk = (chunk + 31) / 32 * 32;
+  if (chunk < 32) chunk = 32;
+  pl.chunk = chunk;
+  pl.n_chunks = (int)((n + chunk - 1) / chunk);
+  if (pl.n_chunks < 1) pl.n_chunks = 1;
+  pl.span_cap = max_windows;
+  return pl;
+}
+
+static int raster_chunk_windows(int n_windows, int n_frames, int H, int W) {
+  const size_t per_window = (size_t)n_frames * H * W * sizeof(uint32_t);
+  size_t c = kKeyPlaneL2Budget / per_window;
+  if (c < 1) c = 1;
+  if (c > (size_t)n_windows) c = n_windows;
+  return (int)c;
+}
+
+}  // namespace egpt
+
+using namespace egpt;
+
+extern "C" size_t egpt_raster_frame_stride(int H, int W) { return align_up((size_t)3 * H * W, 256); }
+
+extern "C" size_t egpt_raster_workspace_bytes(int n_windows, int n_frames, int H, int W) {
+  if (n_windows <= 0 || n_frames <= 0 || H <= 0 || W <= 0) return 0;
+  const int cw = raster_chunk_windows(n_windows, n_frames, H, W);
+  return align_up((size_t)cw * n_frames * H * W * sizeof(uint32_t), 1024) + 1024;
+}
+
+extern "C" int egpt_raster(const void* x, const void* y, const void* p, int x_dtype, int y_dtype, int p_dtype,
+                           const int64_t* window_offsets, int n_windows, int n_frames, int mode, int H, int W,
+                           int fixed_canvas, uint8_t* out_frames, int32_t* out_hw, int32_t* out_counts,
+                           int32_t* status, void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  EGPT_CHECK_ARG(x && y && p && window_offsets && out_frames && out_hw && status && workspace,
+                 "egpt_raster: null pointer argument");
+  EGPT_CHECK_ARG(n_windows > 0 && n_frames > 0, "egpt_raster: n_windows=%d n_frames=%d must be positive", n_windows, n_frames);
+  EGPT_CHECK_ARG(H > 0 && W > 0 && (long long)H * W < (1LL << 31) / 4, "egpt_raster: bad canvas capacity %dx%d", H, W);
+  EGPT_CHECK_ARG(mode == EGPT_RASTER_LAST_WINS || mode == EGPT_RASTER_NEG_WINS, "egpt_raster: unknown mode %d", mode);
+  EGPT_CHECK_ARG(dtype_size(x_dtype) && dtype_size(y_dtype) && dtype_size(p_dtype), "egpt_raster: unknown dtype");
+  EGPT_CHECK_ARG(out_counts == nullptr || mode == EGPT_RASTER_LAST_WINS, "egpt_raster: counts only in LAST_WINS mode");
+  if (workspace_bytes < egpt_raster_workspace_bytes(n_windows, n_frames, H, W)) {
+    set_error("egpt_raster: workspace %zu < %zu bytes", workspace_bytes, egpt_raster_workspace_bytes(n_windows, n_frames, H, W));
+    return EGPT_ERR_WORKSPACE;
+  }
+  const int F = n_windows * n_frames;
+  const size_t frame_stride = egpt_raster_frame_stride(H, W);
+  uint32_t* planes = (uint32_t*)workspace;
+  const bool fast = x_dtype == EGPT_U16 && y_dtype == EGPT_U16 && p_dtype == EGPT_U8 &&
+                    ((uintptr_t)x % 16 == 0) && ((uintptr_t)y % 16 == 0) && ((uintptr_t)p % 8 == 0);
+
+  if (fixed_canvas) {
+    set_fixed_hw_kernel<<<(F + 255) / 256, 256, 0, stream>>>(out_hw, F, H, W);
+    EGPT_LAUNCH_CHECK();
+  } else {
+    EGPT_CUDA(cudaMemsetAsync(out_hw, 0, sizeof(int32_t) * 2 * F, stream));
+  }
+  if (out_counts) EGPT_CUDA(cudaMemsetAsync(out_counts, 0, sizeof(int32_t) * 2 * (size_t)F * H * W, stream));
+
+  const int cw = raster_chunk_windows(n_windows, n_frames, H, W);
+  for (int w0 = 0; w0 < n_windows; w0 += cw) {
+    const int nw = (w0 + cw <= n_windows) ? cw : n_windows - w0;
+    const int slices = nw * n_frames;
+    EGPT_CUDA(cudaMemsetAsync(planes, 0, (size_t)slices * H * W * sizeof(uint32_t), stream));
+    // enough CTAs per slice to fill the machine a few times over
+    int per_slice = (kNumSMs * 8 + slices - 1) / slices;
+    if (per_slice < 1) per_slice = 1;
+    if (per_slice > 64) per_slice = 64;
+    dim3 grid(per_slice, slices);
+    if (fast)
+      raster_scatter_kernel<true><<<grid, kScatterThreads, 0, stream>>>(x, y, p, x_dtype, y_dtype, p_dtype, window_offsets,
+          w0, n_frames, mode, H, W, fixed_canvas, planes, out_hw, out_counts, status);
+    else
+      raster_scatter_kernel<false><<<grid, kScatterThreads, 0, stream>>>(x, y, p, x_dtype, y_dtype, p_dtype, window_offsets,
+          w0, n_frames, mode, H, W, fixed_canvas, planes, out_hw, out_counts, status);
+    EGPT_LAUNCH_CHECK();
+    int cgrid = (int)(((size_t)H * W / 16 + 255) / 256);
+    if (cgrid > 64) cgrid = 64;
+    if (cgrid < 1) cgrid = 1;
+    raster_colourise_kernel<<<dim3(cgrid, slices), 256, 0, stream>>>(planes, out_hw, w0 * n_frames, H, W, out_frames, frame_stride);
+    EGPT_LAUNCH_CHECK();
+  }
+  return EGPT_OK;
+}
+
+extern "C" size_t egpt_split_time_workspace_bytes(int64_t n_events, int max_windows) {
+  if (n_events < 0 || max_windows <= 0) return 0;
+  SplitPlan pl = make_split_plan(n_events, max_windows);
+  return 1024 + align_up((size_t)pl.n_chunks * pl.span_cap * sizeof(int32_t), 1024) +
+         align_up((size_t)pl.span_cap * sizeof(long long), 1024);
+}
+
+extern "C" int egpt_split_time(const void* x, const void* y, const void* t, const void* p, int x_dtype, int y_dtype,
+                               int t_dtype, int p_dtype, int64_t n_events, int64_t interval, void* out_x, void* out_y,
+                               void* out_t, void* out_p, int64_t* out_offsets, int32_t* out_nwindows, int max_windows,
+                               int32_t* status, void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  EGPT_CHECK_ARG(x && y && t && p && out_x && out_y && out_t && out_p && out_offsets && out_nwindows && status && workspace,
+                 "egpt_split_time: null pointer argument");
+  EGPT_CHECK_ARG(n_events > 0 && n_events < (1LL << 31), "egpt_split_time: n_events=%lld out of range", (long long)n_events);
+  EGPT_CHECK_ARG(interval > 0, "egpt_split_time: interval must be positive");
+  EGPT_CHECK_ARG(max_windows > 0 && max_windows <= (1 << 20), "egpt_split_time: max_windows=%d out of range", max_windows);
+  EGPT_CHECK_ARG(dtype_size(x_dtype) && dtype_size(y_dtype) && dtype_size(t_dtype) && dtype_size(p_dtype),
+                 "egpt_split_time: unknown dtype");
+  if (workspace_bytes < egpt_split_time_workspace_bytes(n_events, max_windows)) {
+    set_error("egpt_split_time: workspace too small");
+    return EGPT_ERR_WORKSPACE;
+  }
+  SplitPlan pl = make_split_plan(n_events, max_windows);
+  char* ws = (char*)workspace;
+  long long* minmax = (long long*)ws;
+  int32_t* table = (int32_t*)(ws + 1024);
+  const size_t table_bytes = align_up((size_t)pl.n_chunks * pl.span_cap * sizeof(int32_t), 1024);
+  long long* bin_start = (long long*)(ws + 1024 + table_bytes);
+
+  split_init_kernel<<<1, 1, 0, stream>>>(minmax);
+  EGPT_LAUNCH_CHECK();
+  EGPT_CUDA(cudaMemsetAsync(table, 0, table_bytes, stream));
+  int blocks = (int)((n_events + 1023) / 1024);
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  split_minmax_kernel<<<blocks, 256, 0, stream>>>(t, t_dtype, n_events, interval, minmax);
+  EGPT_LAUNCH_CHECK();
+  const int warps_per_cta = 4;
+  const int cblocks = (pl.n_chunks + warps_per_cta - 1) / warps_per_cta;
+  split_count_kernel<<<cblocks, warps_per_cta * 32, 0, stream>>>(t, t_dtype, pl, interval, minmax, table, status);
+  EGPT_LAUNCH_CHECK();
+  split_scan_kernel<<<1, 1024, 0, stream>>>(pl, minmax, table, bin_start, out_offsets, out_nwindows, max_windows);
+  EGPT_LAUNCH_CHECK();
+  split_scatter_kernel<<<cblocks, warps_per_cta * 32, 0, stream>>>(x, y, t, p, dtype_size(x_dtype), dtype_size(y_dtype),
+      t_dtype, dtype_size(p_dtype), pl, interval, minmax, table, out_x, out_y, out_t, out_p);
+  EGPT_LAUNCH_CHECK();
+  return EGPT_OK;
+}

@@ -1,0 +1,145 @@
+"""Device-side event operators (thin Python over the C ABI): time split, rasterisation,
+CLIP preprocessing.  torch is used only for device memory and streams.
+
+Reference functions replaced: common/common.py:17-37, 64-74, 76-107, 124-127.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import lib, check
+
+CROP = 336
+N_FRAMES = 5                      # hard-coded by the reference caller (common/common.py:119)
+_TORCH_OF_NP = {np.dtype(np.uint8): torch.uint8, np.dtype(np.int8): torch.int8, np.dtype(np.uint16): torch.uint16,
+                np.dtype(np.int16): torch.int16, np.dtype(np.uint32): torch.uint32, np.dtype(np.int32): torch.int32,
+                np.dtype(np.uint64): torch.uint64, np.dtype(np.int64): torch.int64}
+_CODE_OF_TORCH = {torch.uint8: 0, torch.int8: 1, torch.uint16: 2, torch.int16: 3, torch.uint32: 4, torch.int32: 5,
+                  torch.uint64: 6, torch.int64: 7, torch.bool: 0}
+
+
+def _require_cuda(device):
+    if not torch.cuda.is_available():
+        raise _lib.EgptError("eventgpt_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    return torch.device(device if device is not None else "cuda")
+
+
+def stream_ptr(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+class Workspace:
+    """Grow-only device scratch buffers, one set per (device, tag).  The library itself never
+    allocates on the data path; this is the caller-side allocation it asks for."""
+    _bufs = {}
+
+    @classmethod
+    def get(cls, device, tag, nbytes):
+        key = (torch.device(device).index or 0, tag)
+        buf = cls._bufs.get(key)
+        if buf is None or buf.numel() < nbytes:
+            buf = None
+            cls._bufs.pop(key, None)
+            buf = torch.empty(int(nbytes) + 1024, dtype=torch.uint8, device=device)
+            cls._bufs[key] = buf
+        return buf
+
+    @classmethod
+    def clear(cls):
+        cls._bufs.clear()
+
+
+def to_device(arr, device):
+    """numpy integer array (any dtype the reference's .npy files use) -> device tensor, dtype preserved."""
+    if isinstance(arr, torch.Tensor):
+        return arr.to(device).contiguous()
+    a = np.ascontiguousarray(arr)
+    if a.dtype == np.bool_:
+        a = a.view(np.uint8)
+    if a.dtype not in _TORCH_OF_NP:
+        raise TypeError(f"event arrays must be integer typed, got {a.dtype}")
+    return torch.from_numpy(a).to(device, non_blocking=False)
+
+
+def check_status(status, what):
+    """Turns the device status word into the exceptions the reference raises."""
+    flags = int(status.item())
+    if flags & _lib.FLAG_EMPTY_SLICE:
+        # reference: y.max() on an empty slice -> ValueError (common/common.py:65)
+        raise ValueError("zero-size array to reduction operation maximum which has no identity "
+                         f"({what}: a frame slice holds no events)")
+    if flags & _lib.FLAG_OUT_OF_RANGE:
+        raise ValueError(f"{what}: an event coordinate lies outside sensor_size (or is negative)")
+    if flags & _lib.FLAG_TOO_MANY_BINS:
+        raise ValueError(f"{what}: the stream spans more time bins than max_windows")
+    if flags & _lib.FLAG_FILTER_TOO_WIDE:
+        raise ValueError(f"{what}: frame too large for the resize filter (32 taps)")
+
+
+def raster(x, y, p, window_offsets, n_windows, n_frames, H, W, mode=_lib.RASTER_LAST_WINS, fixed_canvas=False,
+           counts=False, status=None):
+    """egpt_raster on device tensors.  Returns (frames uint8 [F, stride], hw int32 [F,2], counts|None, status)."""
+    dev = x.device
+    F = n_windows * n_frames
+    stride = lib().egpt_raster_frame_stride(H, W)
+    frames = torch.empty((F, stride), dtype=torch.uint8, device=dev)
+    hw = torch.empty((F, 2), dtype=torch.int32, device=dev)
+    cnt = torch.empty((F, 2, H, W), dtype=torch.int32, device=dev) if counts else None
+    if status is None:
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+    nws = lib().egpt_raster_workspace_bytes(n_windows, n_frames, H, W)
+    ws = Workspace.get(dev, "raster", nws)
+    check(lib().egpt_raster(ptr(x), ptr(y), ptr(p), _CODE_OF_TORCH[x.dtype], _CODE_OF_TORCH[y.dtype],
+                            _CODE_OF_TORCH[p.dtype], ptr(window_offsets), n_windows, n_frames, mode, H, W,
+                            1 if fixed_canvas else 0, ptr(frames), ptr(hw), ptr(cnt), ptr(status), ptr(ws), ws.numel(),
+                            stream_ptr(dev)), "egpt_raster")
+    return frames, hw, cnt, status
+
+
+def preprocess(frames, hw, max_h, want_pixel_values=True, want_patches=False, status=None):
+    """egpt_preprocess: frames uint8 [F, stride] + hw -> bf16 [F,3,336,336] (and/or im2col patches)."""
+    dev = frames.device
+    F = frames.shape[0]
+    pix = torch.empty((F, 3, CROP, CROP), dtype=torch.bfloat16, device=dev) if want_pixel_values else None
+    patches = torch.empty((F * 576, 640), dtype=torch.bfloat16, device=dev) if want_patches else None
+    if status is None:
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+    nws = lib().egpt_preprocess_workspace_bytes(F, max_h)
+    ws = Workspace.get(dev, "preprocess", nws)
+    check(lib().egpt_preprocess(ptr(frames), frames.stride(0), ptr(hw), F, max_h, ptr(pix), ptr(patches), ptr(status),
+                                ptr(ws), ws.numel(), stream_ptr(dev)), "egpt_preprocess")
+    return pix, patches, status
+
+
+def split_time(x, y, t, p, interval, max_windows=1024, status=None):
+    """egpt_split_time on device tensors.  Returns (x', y', t', p', offsets int64 [max_windows+1], n_windows int32[1], status)."""
+    dev = t.device
+    n = t.numel()
+    ox, oy, ot, op = (torch.empty_like(a) for a in (x, y, t, p))
+    offsets = torch.zeros(max_windows + 1, dtype=torch.int64, device=dev)
+    nwin = torch.zeros(1, dtype=torch.int32, device=dev)
+    if status is None:
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+    nws = lib().egpt_split_time_workspace_bytes(n, max_windows)
+    ws = Workspace.get(dev, "split", nws)
+    check(lib().egpt_split_time(ptr(x), ptr(y), ptr(t), ptr(p), _CODE_OF_TORCH[x.dtype], _CODE_OF_TORCH[y.dtype],
+                                _CODE_OF_TORCH[t.dtype], _CODE_OF_TORCH[p.dtype], n, int(interval), ptr(ox), ptr(oy),
+                                ptr(ot), ptr(op), ptr(offsets), ptr(nwin), max_windows, ptr(status), ptr(ws), ws.numel(),
+                                stream_ptr(dev)), "egpt_split_time")
+    return ox, oy, ot, op, offsets, nwin, status
+
+
+def frames_to_numpy(frames, hw):
+    """Device frame buffer -> list of uint8[H,W,3] ndarrays (what the reference returns)."""
+    hw_h = hw.cpu().numpy()
+    buf = frames.cpu().numpy()
+    out = []
+    for f, (h, w) in enumerate(hw_h):
+        out.append(buf[f, : int(h) * int(w) * 3].reshape(int(h), int(w), 3).copy())
+    return out

@@ -1,0 +1,247 @@
+"""Drop-in for the visual half of the reference's ``model/EventChatModel.py``:
+``VisualTower`` (:45-61), ``visval_encode`` (:194-200), ``feature_adaptor`` (:84-85),
+``get_spatio_temporal_features`` (:15-38) and the event branch of
+``prepare_inputs_labels_for_multimodal`` (:326-345).  Same names, argument meaning and
+error behaviour; the arithmetic runs in libegpt_b200.so.  No CPU fallback.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from . import events as E
+from ._lib import lib, check
+from .weights import VT
+
+TOKENS, HID, LLM = 577, 1024, 4096
+
+
+def get_spatio_temporal_features(features, num_temporal_tokens=None):
+    """model/EventChatModel.py:15-38.  ``features``: list of t tensors [s, c] or a tensor [t, s, c]
+    (bf16 or fp32, on the GPU) -> [num_temporal_tokens + s, c]: temporal rows (mean over s, zero
+    padded / truncated to num_temporal_tokens) first, then the s spatial rows (mean over t)."""
+    if isinstance(features, list):
+        features = torch.stack(features)
+    if features.ndim != 3:
+        raise ValueError("Input features should be a 3D tensor with shape (t, s, c)")
+    return _pool(features[None], num_temporal_tokens)[0]
+
+
+def _pool(features, num_temporal_tokens=None):
+    """[B, t, s, c] -> [B, nt + s, c] through egpt_spatio_temporal_pool."""
+    if not features.is_cuda:
+        raise _lib.EgptError("eventgpt_b200 has no CPU path: features must live on the GPU")
+    B, t, s, c = features.shape
+    nt = t if num_temporal_tokens is None else int(num_temporal_tokens)
+    if features.dtype not in (torch.bfloat16, torch.float32):
+        raise TypeError(f"features must be bf16 or fp32, got {features.dtype}")
+    f = features.contiguous()
+    out = torch.empty((B, nt + s, c), dtype=f.dtype, device=f.device)
+    nws = max(lib().egpt_pool_workspace_bytes(B, t, c), B * ((s + 31) // 32) * t * c * 4)
+    ws = E.Workspace.get(f.device, "pool", nws)
+    check(lib().egpt_spatio_temporal_pool(E.ptr(f), 1 if f.dtype == torch.float32 else 0, B, t, s, c, nt, E.ptr(out),
+                                          E.ptr(ws), ws.numel(), E.stream_ptr(f.device)), "egpt_spatio_temporal_pool")
+    return out
+
+
+class EventProcessor:
+    """Stands where ``CLIPImageProcessor`` does in the reference (``VisualTower.event_processor``,
+    model/EventChatModel.py:55/59; called at common/common.py:125): uint8 HWC frame ->
+    {'pixel_values': [1,3,336,336]}.  The values are the bf16 tensor the reference feeds the model
+    (common/common.py:126), returned as float32 (an exact widening)."""
+    size = {"shortest_edge": 336}
+    crop_size = {"height": 336, "width": 336}
+    image_mean = [0.48145466, 0.4578275, 0.40821073]
+    image_std = [0.26862954, 0.26130258, 0.27577711]
+
+    def __init__(self, device="cuda"):
+        self.device = device
+
+    def __call__(self, images, return_tensors="pt"):
+        if return_tensors != "pt":
+            raise ValueError(f"Unsupported tensor type: {return_tensors}")
+        dev = E._require_cuda(self.device)
+        imgs = images if isinstance(images, (list, tuple)) else [images]
+        outs = []
+        for img in imgs:
+            a = np.ascontiguousarray(np.asarray(img))
+            if a.ndim != 3 or a.shape[2] != 3 or a.dtype != np.uint8:
+                raise ValueError("EventProcessor expects uint8 HWC RGB frames")
+            h, w = a.shape[:2]
+            stride = lib().egpt_raster_frame_stride(h, w)
+            buf = torch.zeros((1, stride), dtype=torch.uint8, device=dev)
+            buf[0, : h * w * 3] = torch.from_numpy(a.reshape(-1)).to(dev)
+            hw = torch.tensor([[h, w]], dtype=torch.int32, device=dev)
+            pix, _, status = E.preprocess(buf, hw, h)
+            E.check_status(status, "EventProcessor")
+            outs.append(pix[0].float())
+        return {"pixel_values": torch.stack(outs)}
+
+    preprocess = __call__
+
+
+class VisualTower:
+    """Role of model/EventChatModel.py:45-61: owns the processor; the tower weights live in the handle."""
+
+    def __init__(self, name, device):
+        self.visual_tower_name = name
+        self.event_processor = EventProcessor(device)
+
+
+class EventGPTVisualFrontEnd:
+    """Everything between an event window and ``event_features [B, 582, 4096]``.
+
+    ``state_dict`` uses the EventGPT checkpoint keys (see eventgpt_b200/weights.py)."""
+
+    def __init__(self, state_dict, device="cuda", num_layers=24, visual_tower="openai/clip-vit-large-patch14-336"):
+        self.device = E._require_cuda(device)
+        self.num_layers = num_layers
+        self.visual_tower = VisualTower(visual_tower, self.device)
+        self._handle = C.c_void_p()
+        with torch.cuda.device(self.device):
+            self._create(state_dict)
+
+    # ---- construction ---------------------------------------------------------------------------
+    def _create(self, sd):
+        dev = self.device
+        keep = []
+
+        def mat(k):
+            t = sd[k].detach().to(dev, torch.bfloat16).contiguous()
+            keep.append(t)
+            return t.data_ptr()
+
+        def vec(k):
+            t = sd[k].detach().to(dev, torch.float32).contiguous()
+            keep.append(t)
+            return t.data_ptr()
+
+        layers = (_lib.LayerWeights * max(1, self.num_layers))()
+        for l in range(self.num_layers):
+            p = f"{VT}encoder.layers.{l}."
+            lw = layers[l]
+            lw.ln1_w, lw.ln1_b = vec(p + "layer_norm1.weight"), vec(p + "layer_norm1.bias")
+            lw.ln2_w, lw.ln2_b = vec(p + "layer_norm2.weight"), vec(p + "layer_norm2.bias")
+            for n, a in (("q", "q"), ("k", "k"), ("v", "v"), ("out", "o")):
+                setattr(lw, a + "_w", mat(p + f"self_attn.{n}_proj.weight"))
+                setattr(lw, a + "_b", vec(p + f"self_attn.{n}_proj.bias"))
+            lw.fc1_w, lw.fc1_b = mat(p + "mlp.fc1.weight"), vec(p + "mlp.fc1.bias")
+            lw.fc2_w, lw.fc2_b = mat(p + "mlp.fc2.weight"), vec(p + "mlp.fc2.bias")
+        w = _lib.Weights()
+        w.num_layers = self.num_layers
+        w.class_embedding = vec(VT + "embeddings.class_embedding")
+        pw = sd[VT + "embeddings.patch_embedding.weight"].detach().reshape(HID, -1)
+        t = pw.to(dev, torch.bfloat16).contiguous()
+        keep.append(t)
+        w.patch_weight = t.data_ptr()
+        w.position_embedding = vec(VT + "embeddings.position_embedding.weight")
+        w.pre_ln_w, w.pre_ln_b = vec(VT + "pre_layrnorm.weight"), vec(VT + "pre_layrnorm.bias")
+        w.layers = layers
+        w.proj0_w, w.proj0_b = mat("model.visual_projector.0.weight"), vec("model.visual_projector.0.bias")
+        w.proj2_w, w.proj2_b = mat("model.visual_projector.2.weight"), vec("model.visual_projector.2.bias")
+        w.adaptor_w, w.adaptor_b = mat("model.feature_adaptor.weight"), vec("model.feature_adaptor.bias")
+        torch.cuda.synchronize(dev)
+        check(lib().egpt_create(C.byref(w), dev.index or 0, C.byref(self._handle)), "egpt_create")
+        del keep
+
+    def close(self):
+        if getattr(self, "_handle", None) and self._handle.value:
+            lib().egpt_destroy(self._handle)
+            self._handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- reference call surface -----------------------------------------------------------------
+    def get_visual_tower(self):
+        return self.visual_tower
+
+    def get_model(self):
+        return self
+
+    def _ws(self, F, tag="tower"):
+        return E.Workspace.get(self.device, tag, lib().egpt_workspace_bytes(F))
+
+    def _bf16(self, x):
+        if not isinstance(x, torch.Tensor) or not x.is_cuda:
+            raise _lib.EgptError("eventgpt_b200 has no CPU path: event tensors must live on the GPU")
+        return x.to(torch.bfloat16).contiguous()
+
+    def tower(self, event_tensor):
+        """CLIPVisionModel(x).last_hidden_state (model/EventChatModel.py:196): [B,3,336,336] -> [B,577,1024]."""
+        x = self._bf16(event_tensor)
+        F = x.shape[0]
+        out = torch.empty((F, TOKENS, HID), dtype=torch.bfloat16, device=x.device)
+        ws = self._ws(F)
+        check(lib().egpt_tower(self._handle, E.ptr(x), F, E.ptr(out), E.ptr(ws), ws.numel(), E.stream_ptr(x.device)),
+              "egpt_tower")
+        return out
+
+    def visval_encode(self, event_tensor):
+        """model/EventChatModel.py:194-200: [B,3,336,336] -> visual_projector(tower(x)) [B,577,4096]."""
+        x = self._bf16(event_tensor)
+        if x.ndim != 4 or tuple(x.shape[1:]) != (3, 336, 336):
+            raise ValueError(f"expected [B,3,336,336], got {tuple(x.shape)}")
+        F = x.shape[0]
+        out = torch.empty((F, TOKENS, LLM), dtype=torch.bfloat16, device=x.device)
+        ws = self._ws(F)
+        check(lib().egpt_visval_encode(self._handle, E.ptr(x), F, E.ptr(out), E.ptr(ws), ws.numel(),
+                                       E.stream_ptr(x.device)), "egpt_visval_encode")
+        return out
+
+    def feature_adaptor(self, x):
+        """model/EventChatModel.py:84-85: Linear(4096, 4096) on the last dimension."""
+        xb = self._bf16(x)
+        rows = xb.numel() // LLM
+        out = torch.empty_like(xb)
+        check(lib().egpt_feature_adaptor(self._handle, E.ptr(xb), rows, E.ptr(out), E.stream_ptr(xb.device)),
+              "egpt_feature_adaptor")
+        return out
+
+    def encode_events(self, event_tensors):
+        """Event branch of prepare_inputs_labels_for_multimodal (model/EventChatModel.py:326-345).
+
+        list of frames / list of lists of frames ([3,336,336] each) -> event_features [B, n+577, 4096]
+        (tower, projector, adaptor, pooling);  a plain tensor [B,3,336,336] -> visval_encode only
+        (no adaptor, no pooling), exactly as the reference's tensor branch."""
+        if not isinstance(event_tensors, list):
+            return self.visval_encode(event_tensors)
+        if not all(isinstance(item, list) for item in event_tensors):
+            event_tensors = [event_tensors]
+        n = len(event_tensors[0])
+        if any(len(item) != n for item in event_tensors):
+            # torch.stack at :343 would fail on ragged frame counts in the reference too
+            raise RuntimeError("stack expects each sample to hold the same number of event frames")
+        B = len(event_tensors)
+        x = self._bf16(torch.stack([torch.stack([ev for ev in item]) for item in event_tensors]).reshape(B * n, 3, 336, 336))
+        out = torch.empty((B, n + TOKENS, LLM), dtype=torch.bfloat16, device=x.device)
+        ws = self._ws(B * n)
+        check(lib().egpt_encode_pool(self._handle, E.ptr(x), B, n, E.ptr(out), E.ptr(ws), ws.numel(),
+                                     E.stream_ptr(x.device)), "egpt_encode_pool")
+        return out
+
+    # ---- fused path: events -> tokens ------------------------------------------------------------
+    def visual_tokens(self, x, y, p, window_offsets, sensor_size, n_frames=E.N_FRAMES, out=None, check_flags=True):
+        """process_event_data (common/common.py:110-129) + the list branch (:326-343) for a batch of
+        windows, device resident end to end.  x, y, p: device integer tensors holding all windows back
+        to back; window_offsets: int64 [B+1] on the device.  Returns tokens bf16 [B, n_frames+577, 4096]."""
+        dev = x.device
+        H, W = int(sensor_size[0]), int(sensor_size[1])
+        B = window_offsets.numel() - 1
+        if out is None:
+            out = torch.empty((B, n_frames + TOKENS, LLM), dtype=torch.bfloat16, device=dev)
+        hw = torch.empty((B * n_frames, 2), dtype=torch.int32, device=dev)
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+        nws = lib().egpt_visual_tokens_workspace_bytes(B, n_frames, H, W)
+        ws = E.Workspace.get(dev, "fused", nws)
+        check(lib().egpt_visual_tokens(self._handle, E.ptr(x), E.ptr(y), E.ptr(p), E._CODE_OF_TORCH[x.dtype],
+                                       E._CODE_OF_TORCH[y.dtype], E._CODE_OF_TORCH[p.dtype], E.ptr(window_offsets), B,
+                                       n_frames, H, W, E.ptr(out), E.ptr(hw), E.ptr(status), E.ptr(ws), ws.numel(),
+                                       E.stream_ptr(dev)), "egpt_visual_tokens")
+        if check_flags:
+            E.check_status(status, "visual_tokens")
+        return out
