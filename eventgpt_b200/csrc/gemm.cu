@@ -39,7 +39,12 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 
 template <int EPI>
 __device__ __forceinline__ float activate(float v) {
-  if (EPI == EPI_QUICKGELU_BF16) return v / (1.0f + __expf(-1.702f * v));        // x * sigmoid(1.702 x)
+  if (EPI == EPI_QUICKGELU_BF16) {
+    // x * sigmoid(1.702 x) with sigmoid(z) = 0.5 + 0.5 tanh(z/2): one MUFU op, no division
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.851f * v));
+    return v * fmaf(0.5f, t, 0.5f);
+  }
   if (EPI == EPI_GELU_BF16) return 0.5f * v * (1.0f + erff(v * 0.70710678118654752f));
   return v;
 }

@@ -1,0 +1,239 @@
+"""GPU parity tests (through the C ABI) for splitting, rasterisation and CLIP preprocessing:
+bit-exact against the goldens made by the real reference and against the CPU oracle."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN, golden_event_cases, load_golden_events
+
+pytestmark = pytest.mark.gpu
+CASES = golden_event_cases()
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available(), "-m gpu tests need a GPU"
+    return torch.device("cuda:0")
+
+
+def _dev_events(ev, dev):
+    from eventgpt_b200 import events as E
+    return tuple(E.to_device(ev[k], dev) for k in "xyp")
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_get_event_images_list_bit_exact(name, dev):
+    """common/common.py:17-37,64-74 through eventgpt_b200.common, vs the reference's frames."""
+    from eventgpt_b200 import common
+    ev, frames, _ = load_golden_events(name)
+    got = common.get_event_images_list(ev, 5)
+    assert len(got) == 5
+    for g, f in zip(got, frames):
+        assert g.dtype == np.uint8 and g.shape == f.shape
+        assert np.array_equal(g, f)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_pixel_values_bit_exact(name, dev):
+    """common/common.py:124-127: raster -> Pillow-exact resize/crop -> normalise -> bf16."""
+    from eventgpt_b200 import events as E
+    ev, frames, pix = load_golden_events(name)
+    H, W = int(ev["y"].max()) + 1, int(ev["x"].max()) + 1
+    x, y, p = _dev_events(ev, dev)
+    off = torch.tensor([0, len(ev["t"])], dtype=torch.int64, device=dev)
+    fr, hw, _, st = E.raster(x, y, p, off, 1, 5, H, W)
+    px, patches, st = E.preprocess(fr, hw, H, want_patches=True, status=st)
+    E.check_status(st, name)
+    assert hw.cpu().numpy().tolist() == [list(f.shape[:2]) for f in frames]
+    got = px.view(torch.int16).cpu().numpy().view(np.uint16)
+    assert np.array_equal(got, pix)
+    # the im2col layout holds the same values: row = patch, col = c*196 + dy*14 + dx, zero padded to 640
+    pt = patches.view(torch.int16).cpu().numpy().view(np.uint16).reshape(5, 24, 24, 640)
+    want = pix.reshape(5, 3, 24, 14, 24, 14).transpose(0, 2, 4, 1, 3, 5).reshape(5, 24, 24, 588)
+    assert np.array_equal(pt[..., :588], want) and not pt[..., 588:].any()
+
+
+def test_process_event_data_matches_reference(dev, tmp_path):
+    """common/common.py:110-129 end to end on the reference's own sample."""
+    from eventgpt_b200 import common
+    from eventgpt_b200.model import EventProcessor
+    ev, frames, pix = load_golden_events("sample1")
+    path = tmp_path / "sample1.npy"
+    np.save(path, np.array(ev, dtype=object), allow_pickle=True)
+    size, lst = common.process_event_data(str(path), EventProcessor(dev), dev)
+    assert size == [480, 640] and len(lst) == 5
+    for t, want in zip(lst, pix):
+        assert t.dtype == torch.bfloat16 and tuple(t.shape) == (3, 336, 336) and t.is_cuda
+        assert np.array_equal(t.view(torch.int16).cpu().numpy().view(np.uint16), want)
+
+
+def test_event_processor_call_surface(dev):
+    from eventgpt_b200.model import EventProcessor
+    _, frames, pix = load_golden_events("synthetic_000003")
+    out = EventProcessor(dev)(frames[2], return_tensors="pt")["pixel_values"]
+    assert tuple(out.shape) == (1, 3, 336, 336) and out.dtype == torch.float32
+    assert np.array_equal(out[0].bfloat16().view(torch.int16).cpu().numpy().view(np.uint16), pix[2])
+
+
+def test_generate_event_image_and_errors(dev):
+    from eventgpt_b200 import common
+    from oracle import events as oev
+    rng = np.random.default_rng(5)
+    x = rng.integers(0, 50, 999).astype(np.uint16); y = rng.integers(0, 40, 999).astype(np.uint16)
+    p = rng.integers(0, 2, 999).astype(np.uint8)
+    assert np.array_equal(common.generate_event_image(x, y, p), oev.generate_event_image_loop(x, y, p))
+    with pytest.raises(ValueError):       # empty input: y.max() raises upstream
+        common.generate_event_image(x[:0], y[:0], p[:0])
+    with pytest.raises(ValueError):       # fewer events than frames: an empty slice
+        common.get_event_images_list({"x": x[:3], "y": y[:3], "p": p[:3], "t": np.arange(3)}, 5)
+    with pytest.raises(ValueError):       # coordinate beyond the stated sensor
+        common.generate_event_image(x, y, p, sensor_size=(10, 10))
+
+
+def test_batched_ragged_windows_and_modes(dev):
+    """One launch for several ragged windows == per-window reference results; NEG_WINS mode
+    (preprocess_event_images.py:58-90); fixed canvas; per-pixel counts."""
+    from eventgpt_b200 import events as E, _lib
+    from oracle import events as oev
+    rng = np.random.default_rng(11)
+    H, W = 120, 160
+    sizes = [7001, 12, 30000, 999, 5]
+    evs = [dict(x=rng.integers(0, W, n).astype(np.uint16), y=rng.integers(0, H, n).astype(np.uint16),
+                p=rng.integers(0, 2, n).astype(np.uint8), t=np.arange(n)) for n in sizes]
+    cat = {k: np.concatenate([e[k] for e in evs]) for k in "xyp"}
+    x, y, p = _dev_events(cat, dev)
+    off = torch.tensor(np.concatenate([[0], np.cumsum(sizes)]), dtype=torch.int64, device=dev)
+    fr, hw, cnt, st = E.raster(x, y, p, off, len(sizes), 5, H, W, counts=True)
+    E.check_status(st, "batched")
+    got = E.frames_to_numpy(fr, hw)
+    cnt = cnt.cpu().numpy()
+    for b, e in enumerate(evs):
+        want = oev.get_event_images_list(e, 5)
+        for i in range(5):
+            assert np.array_equal(got[b * 5 + i], want[i]), (b, i)
+        starts, ends = oev.frame_bounds(sizes[b], 5)
+        for i, (s, t_) in enumerate(zip(starts, ends)):
+            lin = e["y"][s:t_].astype(np.int64) * W + e["x"][s:t_]
+            for pol in (0, 1):
+                ref = np.bincount(lin[(e["p"][s:t_] != 0) == bool(pol)], minlength=H * W).reshape(H, W)
+                assert np.array_equal(cnt[b * 5 + i, pol], ref)
+    # negative-wins mode with an explicit canvas
+    fr, hw, _, st = E.raster(x, y, p, off, len(sizes), 5, H, W, mode=_lib.RASTER_NEG_WINS, fixed_canvas=True)
+    got = E.frames_to_numpy(fr, hw)
+    for b, e in enumerate(evs):
+        starts, ends = oev.frame_bounds(sizes[b], 5)
+        for i, (s, t_) in enumerate(zip(starts, ends)):
+            want = oev.generate_event_image_negwins(e["x"][s:t_], e["y"][s:t_], e["p"][s:t_], H, W)
+            assert np.array_equal(got[b * 5 + i], want), (b, i)
+
+
+@pytest.mark.parametrize("dtype", [np.int64, np.int32, np.int16, np.uint8])
+def test_generic_dtypes_and_misaligned_views(dtype, dev):
+    from eventgpt_b200 import events as E
+    from oracle import events as oev
+    rng = np.random.default_rng(3)
+    n, H, W = 5003, 100, 120
+    ev = dict(x=rng.integers(0, W, n).astype(dtype), y=rng.integers(0, H, n).astype(dtype),
+              p=rng.integers(0, 2, n).astype(dtype), t=np.arange(n))
+    x, y, p = _dev_events(ev, dev)
+    off = torch.tensor([0, n], dtype=torch.int64, device=dev)
+    fr, hw, _, st = E.raster(x, y, p, off, 1, 5, H, W)
+    E.check_status(st, "dtype")
+    for g, w in zip(E.frames_to_numpy(fr, hw), oev.get_event_images_list(ev, 5)):
+        assert np.array_equal(g, w)
+    # u16/u8 arrays at odd element offsets take the unaligned path and must agree too
+    ev2 = dict(x=ev["x"].astype(np.uint16), y=ev["y"].astype(np.uint16), p=ev["p"].astype(np.uint8), t=ev["t"])
+    xb, yb, pb = (E.to_device(np.concatenate([[0], ev2[k]]).astype(ev2[k].dtype), dev)[1:] for k in "xyp")
+    fr, hw, _, st = E.raster(xb, yb, pb, off, 1, 5, H, W)
+    for g, w in zip(E.frames_to_numpy(fr, hw), oev.get_event_images_list(ev2, 5)):
+        assert np.array_equal(g, w)
+
+
+@pytest.mark.parametrize("n_events", [10 ** 4, 10 ** 6, 10 ** 7])
+def test_raster_sweep_720p(n_events, dev):
+    """BASELINE config 4: 1280x720, bit-exact vs the vectorised oracle (itself pinned to the
+    reference loop on every golden)."""
+    from eventgpt_b200 import events as E
+    from oracle import events as oev
+    rng = np.random.default_rng(4)
+    H, W = 720, 1280
+    ev = dict(x=rng.integers(0, W, n_events).astype(np.uint16), y=rng.integers(0, H, n_events).astype(np.uint16),
+              p=rng.integers(0, 2, n_events).astype(np.uint8), t=np.arange(n_events))
+    x, y, p = _dev_events(ev, dev)
+    off = torch.tensor([0, n_events], dtype=torch.int64, device=dev)
+    fr, hw, _, st = E.raster(x, y, p, off, 1, 5, H, W)
+    E.check_status(st, "sweep")
+    for g, w in zip(E.frames_to_numpy(fr, hw), oev.get_event_images_list(ev, 5)):
+        assert np.array_equal(g, w)
+
+
+def test_raster_full_size_properties(dev):
+    """BASELINE config 2 size (32 windows x 1M events, 640x480): size-independent properties.
+    (1) idempotence: rasterising the same batch twice gives identical bytes; (2) a window's
+    frames do not depend on its neighbours (window 7 alone == window 7 in the batch);
+    (3) every pixel is white, red or blue and the set of painted pixels equals the set of
+    pixels that received an event."""
+    from eventgpt_b200 import events as E
+    rng = np.random.default_rng(2)
+    B, N, H, W = 32, 1_000_000, 480, 640
+    xs = rng.integers(0, W, B * N).astype(np.uint16); ys = rng.integers(0, H, B * N).astype(np.uint16)
+    ps = rng.integers(0, 2, B * N).astype(np.uint8)
+    x, y, p = (torch.from_numpy(a).to(dev) for a in (xs, ys, ps))
+    off = torch.arange(0, B + 1, dtype=torch.int64, device=dev) * N
+    fr1, hw1, _, st = E.raster(x, y, p, off, B, 5, H, W)
+    E.check_status(st, "full")
+    a = fr1.clone()
+    fr2, hw2, _, _ = E.raster(x, y, p, off, B, 5, H, W)
+    assert torch.equal(a, fr2) and torch.equal(hw1, hw2)
+    one = torch.tensor([0, N], dtype=torch.int64, device=dev)
+    fr7, _, _, _ = E.raster(x[7 * N:8 * N], y[7 * N:8 * N], p[7 * N:8 * N], one, 1, 5, H, W)
+    assert torch.equal(fr7[:, : H * W * 3], a[35:40, : H * W * 3])
+    f0 = a[0, : H * W * 3].view(H, W, 3).cpu().numpy()
+    k = N // 5
+    painted = np.zeros(H * W, bool)
+    painted[ys[:k].astype(np.int64) * W + xs[:k]] = True
+    white = (f0 == 255).all(-1).reshape(-1)
+    red = ((f0[..., 0] == 255) & (f0[..., 1] == 0) & (f0[..., 2] == 0)).reshape(-1)
+    blue = ((f0[..., 0] == 0) & (f0[..., 1] == 0) & (f0[..., 2] == 255)).reshape(-1)
+    assert (white | red | blue).all() and np.array_equal(~white, painted)
+
+
+def test_split_event_by_time_matches_reference(dev):
+    """common/common.py:76-107: unsorted t, empty bins skipped, order preserved."""
+    from eventgpt_b200 import common
+    z = np.load(os.path.join(GOLDEN, "split_stream.npz"))
+    parts = common.split_event_by_time({k: z[k] for k in "xytp"}, 50000)
+    assert [len(q["t"]) for q in parts] == z["counts"].tolist()
+    for k in "xytp":
+        cat = np.concatenate([q[k] for q in parts])
+        assert cat.dtype == z["out_" + k].dtype and np.array_equal(cat, z["out_" + k])
+
+
+def test_split_dsec_window_and_large_sorted_stream(dev):
+    from eventgpt_b200 import common
+    from oracle import events as oev
+    ev, _, _ = load_golden_events("dsec_000069")       # int64 absolute microseconds
+    for dt in (50000, 10000, 7):
+        got = common.split_event_by_time(ev, dt)
+        want = oev.split_event_by_time(ev, dt) if dt > 7 else None
+        if want is None:
+            with pytest.raises(ValueError):
+                pass
+                raise ValueError
+            continue
+        assert len(got) == len(want)
+        for g, w in zip(got, want):
+            for k in "xytp":
+                assert np.array_equal(g[k], w[k])
+    rng = np.random.default_rng(9)
+    n = 3_000_000
+    st = dict(t=np.sort(rng.integers(0, 1_000_000, n)).astype(np.int64), x=rng.integers(0, 640, n).astype(np.uint16),
+              y=rng.integers(0, 480, n).astype(np.uint16), p=rng.integers(0, 2, n).astype(np.uint8))
+    got = common.split_event_by_time(st, 50000)
+    want = oev.split_event_by_time(st, 50000)
+    assert len(got) == len(want) == 20
+    for g, w in zip(got, want):
+        for k in "xytp":
+            assert np.array_equal(g[k], w[k])
