@@ -50,6 +50,8 @@ SIGNATURES = {
     "egpt_last_error": (C.c_char_p, []),
     "egpt_version": (_i, []),
     "egpt_launch_count": (_i64, [_i]),
+    "egpt_profile_enable": (_i, [_i]),
+    "egpt_profile_collect": (_i, [_vp, _vp, _vp]),
     "egpt_split_time_workspace_bytes": (_sz, [_i64, _i]),
     "egpt_split_time": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i,
                              _vp, _vp, _sz, _vp]),
@@ -103,3 +105,19 @@ def check(rc, what=""):
 
 def launch_count(reset=False):
     return int(lib().egpt_launch_count(1 if reset else 0))
+
+
+PROFILE_CATEGORIES = ("gemm", "attention", "elementwise", "raster", "preprocess", "pool", "split", "other")
+
+
+def profile_enable(on=True):
+    check(lib().egpt_profile_enable(1 if on else 0), "egpt_profile_enable")
+
+
+def profile_collect():
+    """{category: (device ms, launches, algorithmic work)} since the last collect (synchronises)."""
+    ms = (C.c_double * 8)()
+    n = (C.c_int64 * 8)()
+    w = (C.c_double * 8)()
+    check(lib().egpt_profile_collect(ms, n, w), "egpt_profile_collect")
+    return {name: (ms[i], int(n[i]), w[i]) for i, name in enumerate(PROFILE_CATEGORIES)}

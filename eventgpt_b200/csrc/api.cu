@@ -16,6 +16,23 @@ void set_error(const char* fmt, ...) {
 }
 void count_launch(int n) { g_launches += n; }
 
+struct ProfRec { int cat; double work; cudaEvent_t a, b; };
+static thread_local bool g_prof_on = false;
+static thread_local std::vector<ProfRec>* g_prof = nullptr;
+void prof_begin(int category, double work, cudaStream_t stream) {
+  if (!g_prof_on) return;
+  if (!g_prof) g_prof = new std::vector<ProfRec>();
+  ProfRec r{category, work, nullptr, nullptr};
+  cudaEventCreate(&r.a);
+  cudaEventCreate(&r.b);
+  cudaEventRecord(r.a, stream);
+  g_prof->push_back(r);
+}
+void prof_end(cudaStream_t stream) {
+  if (!g_prof_on || !g_prof || g_prof->empty()) return;
+  cudaEventRecord(g_prof->back().b, stream);
+}
+
 // kernels implemented in the other translation units
 int gemm_bf16(const void* A, const void* B, const float* bias, void* out, long long M, int N, int K, int epilogue, cudaStream_t);
 int attention(const void* qkv, int n_frames_total, void* out, cudaStream_t);
@@ -146,6 +163,27 @@ extern "C" int64_t egpt_launch_count(int reset) {
   const long long v = g_launches;
   if (reset) g_launches = 0;
   return v;
+}
+
+extern "C" int egpt_profile_enable(int on) {
+  g_prof_on = on != 0;
+  return EGPT_OK;
+}
+extern "C" int egpt_profile_collect(double* ms, int64_t* launches, double* work) {
+  EGPT_CHECK_ARG(ms && launches && work, "egpt_profile_collect: null argument");
+  for (int i = 0; i < EGPT_PROFILE_CATEGORIES; ++i) { ms[i] = 0; launches[i] = 0; work[i] = 0; }
+  if (!g_prof) return EGPT_OK;
+  for (ProfRec& r : *g_prof) {
+    float t = 0.f;
+    if (cudaEventSynchronize(r.b) == cudaSuccess && cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess &&
+        r.cat >= 0 && r.cat < EGPT_PROFILE_CATEGORIES) {
+      ms[r.cat] += t; launches[r.cat] += 1; work[r.cat] += r.work;
+    }
+    cudaEventDestroy(r.a);
+    cudaEventDestroy(r.b);
+  }
+  g_prof->clear();
+  return EGPT_OK;
 }
 
 extern "C" int egpt_create(const egpt_weights* wh, int device, egpt_handle** out) {

@@ -179,6 +179,7 @@ int attention(const void* qkv, int n_frames_total, void* out, cudaStream_t strea
     EGPT_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
     attr_set = true;
   }
+  ProfScope prof(PROF_ATTN, 4.0 * kS * kS * kD * kHeads * (double)n_frames_total, stream);
   attention_kernel<<<n_frames_total * kHeads, kAttnThreads, kAttnSmem, stream>>>(
       reinterpret_cast<const __nv_bfloat16*>(qkv), reinterpret_cast<__nv_bfloat16*>(out));
   EGPT_LAUNCH_CHECK();

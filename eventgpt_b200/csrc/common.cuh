@@ -12,6 +12,17 @@ namespace egpt {
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
 
+// optional per-kernel-family event timing (egpt_profile_enable / egpt_profile_collect)
+enum { PROF_GEMM = 0, PROF_ATTN = 1, PROF_ELEMENTWISE = 2, PROF_RASTER = 3, PROF_PREPROCESS = 4, PROF_POOL = 5,
+       PROF_SPLIT = 6 };
+void prof_begin(int category, double work, cudaStream_t stream);
+void prof_end(cudaStream_t stream);
+struct ProfScope {
+  cudaStream_t st;
+  ProfScope(int category, double work, cudaStream_t s) : st(s) { prof_begin(category, work, s); }
+  ~ProfScope() { prof_end(st); }
+};
+
 #define EGPT_CHECK_ARG(cond, ...)                      \
   do {                                                 \
     if (!(cond)) {                                     \

@@ -225,18 +225,21 @@ __global__ void pad_patch_weight_kernel(const __nv_bfloat16* __restrict__ in, __
 
 // ---- launchers -----------------------------------------------------------------------------------
 int layernorm_bf16(const float* h, const float* gamma, const float* beta, void* y, long long rows, cudaStream_t st) {
+  ProfScope prof(PROF_ELEMENTWISE, (double)rows * kHid * 6, st);
   layernorm_bf16_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(h, gamma, beta, (__nv_bfloat16*)y, rows);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
 }
 int embed_preln(const float* patch, const float* cls, const float* pos, const float* gamma, const float* beta, float* h,
                 long long rows, cudaStream_t st) {
+  ProfScope prof(PROF_ELEMENTWISE, (double)rows * kHid * 8, st);
   embed_preln_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(patch, cls, pos, gamma, beta, h, rows);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
 }
 int f32_to_bf16(const float* in, void* out, long long n, cudaStream_t st) {
   const long long n8 = n / 8;
+  ProfScope prof(PROF_ELEMENTWISE, (double)n * 6, st);
   long long blocks = (n8 + 255) / 256;
   if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
   f32_to_bf16_kernel<<<(unsigned)blocks, 256, 0, st>>>(in, (__nv_bfloat16*)out, n8);
@@ -245,6 +248,7 @@ int f32_to_bf16(const float* in, void* out, long long n, cudaStream_t st) {
 }
 int im2col(const uint16_t* pix, uint16_t* patches, int F, cudaStream_t st) {
   const long long total = (long long)F * 576 * 640;
+  ProfScope prof(PROF_ELEMENTWISE, (double)F * 3 * 336 * 336 * 2 + (double)total * 2, st);
   long long blocks = (total + 255) / 256;
   if (blocks > kNumSMs * 32) blocks = kNumSMs * 32;
   im2col_kernel<<<(unsigned)blocks, 256, 0, st>>>(pix, patches, total);
@@ -292,6 +296,8 @@ extern "C" int egpt_spatio_temporal_pool(const void* features, int is_f32, int b
   const size_t need = (size_t)batch * chunks * t * c * sizeof(float);
   if (workspace_bytes < need) { set_error("egpt_spatio_temporal_pool: workspace %zu < %zu", workspace_bytes, need); return EGPT_ERR_WORKSPACE; }
   float* partial = (float*)workspace;
+  const double esz = is_f32 ? 4.0 : 2.0;
+  ProfScope prof(PROF_POOL, ((double)batch * t * s * c + (double)batch * (n_temporal + s) * c) * esz, st);
   dim3 grid((c / 8 + 127) / 128, chunks, batch);
   const long long total = (long long)batch * n_temporal * c;
   if (is_f32) {

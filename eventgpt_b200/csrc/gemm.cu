@@ -245,6 +245,7 @@ int gemm_bf16(const void* A, const void* B, const float* bias, void* out, long l
   EGPT_CHECK_ARG(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
                  (bias == nullptr || (uintptr_t)bias % 16 == 0), "gemm: pointers must be 16-byte aligned");
   CUtensorMap ta, tb;
+  ProfScope prof(PROF_GEMM, 2.0 * (double)M * N * K, stream);
   EGPT_TRY(make_tmap_bf16(&ta, A, (uint64_t)M, (uint64_t)K, BM));
   EGPT_TRY(make_tmap_bf16(&tb, B, (uint64_t)N, (uint64_t)K, BN));
   switch (epilogue) {

@@ -233,6 +233,7 @@ extern "C" int egpt_preprocess(const uint8_t* frames, size_t frame_stride, const
     return EGPT_ERR_WORKSPACE;
   }
   const int F = n_frames_total;
+  ProfScope prof(PROF_PREPROCESS, 0.0, stream);
   int32_t* tables = (int32_t*)workspace;
   uint8_t* tmp = (uint8_t*)workspace + tables_bytes(F);
   const size_t tmp_stride = tmp_stride_bytes(max_h);

@@ -406,6 +406,9 @@ extern "C" int egpt_raster(const void* x, const void* y, const void* p, int x_dt
   }
   const int F = n_windows * n_frames;
   const size_t frame_stride = egpt_raster_frame_stride(H, W);
+  // algorithmic bytes are data dependent (5 B/event + 3 B/pixel written); the caller of
+  // egpt_profile_collect supplies them, so only time is recorded here
+  ProfScope prof(PROF_RASTER, 0.0, stream);
   uint32_t* planes = (uint32_t*)workspace;
   const bool fast = x_dtype == EGPT_U16 && y_dtype == EGPT_U16 && p_dtype == EGPT_U8 &&
                     ((uintptr_t)x % 16 == 0) && ((uintptr_t)y % 16 == 0) && ((uintptr_t)p % 8 == 0);
@@ -468,6 +471,8 @@ extern "C" int egpt_split_time(const void* x, const void* y, const void* t, cons
     return EGPT_ERR_WORKSPACE;
   }
   SplitPlan pl = make_split_plan(n_events, max_windows);
+  ProfScope prof(PROF_SPLIT, 2.0 * (double)n_events * (dtype_size(x_dtype) + dtype_size(y_dtype) + dtype_size(t_dtype) +
+                                                        dtype_size(p_dtype)) + 2.0 * (double)n_events * dtype_size(t_dtype), stream);
   char* ws = (char*)workspace;
   long long* minmax = (long long*)ws;
   int32_t* table = (int32_t*)(ws + 1024);

@@ -201,6 +201,16 @@ int egpt_attention(const uint16_t* qkv, int n_frames_total, uint16_t* out, void*
 /* number of kernel launches issued by this library on the calling thread since the last reset   */
 int64_t egpt_launch_count(int reset);
 
+/* Measurement aid (no counterpart in the reference): while enabled on the calling thread, every  */
+/* kernel family launch is bracketed by CUDA events on its own stream.  egpt_profile_collect      */
+/* synchronises those events, adds up per category {0 gemm, 1 attention, 2 layernorm/elementwise, */
+/* 3 raster, 4 preprocess, 5 pooling, 6 split} the device milliseconds, the launches and the      */
+/* algorithmic work (FLOPs for 0-1, bytes for 2-6), writes three arrays of EGPT_PROFILE_CATEGORIES */
+/* entries and clears the record.                                                                 */
+#define EGPT_PROFILE_CATEGORIES 8
+int egpt_profile_enable(int on);
+int egpt_profile_collect(double* ms, int64_t* launches, double* work);
+
 #ifdef __cplusplus
 }
 #endif
