@@ -65,7 +65,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.index)], stdout=open(self.path, "w"),
+                                          "-lms", "50", "-i", str(self.index)], stdout=open(self.path, "w"),
                                          stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
@@ -214,13 +214,13 @@ def run_ours(args, rank, world, local_rank):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()                      # nvidia-smi needs ~1 s to start: launched before the warm-up
     for _ in range(args.warmup):
         step_resident()
     fe.visual_tokens(dx, dy, dp, doff, (H, W), out=tokens, check_flags=True)     # raises on any device-side flag
     _lib.launch_count(True)
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
     total_ms = timed(step_resident, args.steps)
     clocks = sampler.stop() if rank == 0 else None
     launches = _lib.launch_count(True)

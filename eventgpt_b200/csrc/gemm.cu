@@ -12,8 +12,10 @@
 //   warp 1    MMA issuer: one thread issues tcgen05.mma (M128 N256 K16), fp32
 //             accumulators in TMEM, double-buffered (2 x 256 columns)
 //   warp 2    TMEM allocator
-//   warps 4-7 epilogue: tcgen05.ld 32 lanes x 32 columns -> bias / activation /
-//             fp32 residual add -> global
+//   warps 4-7 epilogue: tcgen05.ld 32 lanes x 32 columns -> bias / activation -> 128-byte
+//             swizzled staging rows in shared memory -> TMA store (bf16 / fp32), or TMA
+//             reduce-add for the fp32 residual stream (h += acc + bias is done in L2;
+//             the SM never reads h).  Rows past M are clipped by the TMA unit.
 // Tiles are walked n-fastest so the CTAs running concurrently share A rows through L2.
 #include "common.cuh"
 #include "sm100_ptx.cuh"
@@ -28,7 +30,8 @@ constexpr int kBBytes = BN * BK * 2;               // 32 KB
 constexpr int kStageBytes = kABytes + kBBytes;     // 48 KB
 constexpr int kTmemCols = 2 * BN;                  // two accumulator stages
 constexpr int kGemmThreads = 256;
-constexpr int kGemmSmem = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int kStagingBytes = 4 * 2 * 4096;        // 4 epilogue warps x 2 buffers x (32 rows x 128 B)
+constexpr int kGemmSmem = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 
 enum { EPI_BIAS_BF16 = 0, EPI_QUICKGELU_BF16 = 1, EPI_GELU_BF16 = 2, EPI_RESIDUAL_F32 = 3, EPI_STORE_F32 = 4 };
 
@@ -52,10 +55,11 @@ __device__ __forceinline__ float activate(float v) {
 template <int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                 const float* __restrict__ bias, void* __restrict__ out, long long M, int N, int K) {
+                 const __grid_constant__ CUtensorMap tmap_out, const float* __restrict__ bias, long long M, int N, int K) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+  uint8_t* staging = smem + kStages * kStageBytes;                 // 1024-byte aligned
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + kStagingBytes);
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tmem_full = empty_bar + kStages;
   uint64_t* tmem_empty = tmem_full + 2;
@@ -70,6 +74,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tmap_a);
     ptx::prefetch_tensormap(&tmap_b);
+    ptx::prefetch_tensormap(&tmap_out);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages; ++i) { ptx::mbar_init(full_bar + i, 1); ptx::mbar_init(empty_bar + i, 1); }
@@ -127,59 +132,69 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   } else if (warp >= 4) {
     // ===== epilogue =====
     const int q = warp & 3;                            // TMEM lane quadrant this warp may read
-    int acc = 0; uint32_t acc_phase = 0;
+    constexpr bool kF32Out = (EPI == EPI_RESIDUAL_F32 || EPI == EPI_STORE_F32);
+    constexpr int CH = kF32Out ? 32 : 64;              // columns per staged chunk (128 B per row)
+    uint8_t* my_stage = staging + q * 8192;
+    const uint32_t sw = (uint32_t)(lane & 7);          // SWIZZLE_128B: 16-byte chunk index ^= row & 7
+    int acc = 0; uint32_t acc_phase = 0; int buf = 0;
     for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const long long row = (tile / n_tiles) * BM + q * 32 + lane;
+      const int row0 = (int)(tile / n_tiles) * BM + q * 32;
       const int n0 = (int)(tile % n_tiles) * BN;
       ptx::mbar_wait(tmem_full + acc, acc_phase);
       ptx::tcgen05_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t r[32];
-        ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, r);
+      for (int c0 = 0; c0 < BN; c0 += CH) {
+        uint32_t r[CH];
+        ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+        if (CH == 64) ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0 + 32u, *reinterpret_cast<uint32_t(*)[32]>(&r[CH - 32]));
         ptx::tmem_ld_wait();
-        if (row < M) {
-          float v[32];
+        if (c0 + CH == BN) {                           // accumulator fully read: hand it back to the MMA warp
+          ptx::tcgen05_fence_before();
+          ptx::mbar_arrive(tmem_empty + acc);
+        }
+        // the TMA store that last used this staging buffer must have finished reading it
+        if (lane == 0) ptx::bulk_wait_group_read<1>();
+        __syncwarp();
+        uint8_t* dst = my_stage + buf * 4096 + lane * 128;
+        if (bias != nullptr) {
+          const float4* bp = reinterpret_cast<const float4*>(bias + n0 + c0);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          if (bias != nullptr) {
-            const float4* bp = reinterpret_cast<const float4*>(bias + n0 + c0);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float4 b = __ldg(bp + j);
-              v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
-            }
-          }
-          if (EPI == EPI_RESIDUAL_F32 || EPI == EPI_STORE_F32) {
-            float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + row * N + n0 + c0);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              float4 o = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-              if (EPI == EPI_RESIDUAL_F32) {
-                const float4 h = op[j];
-                o.x += h.x; o.y += h.y; o.z += h.z; o.w += h.w;
-              }
-              op[j] = o;
-            }
-          } else {
-            uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(out) + row * N + n0 + c0);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              uint4 o;
-              o.x = pack_bf16(activate<EPI>(v[8 * j + 0]), activate<EPI>(v[8 * j + 1]));
-              o.y = pack_bf16(activate<EPI>(v[8 * j + 2]), activate<EPI>(v[8 * j + 3]));
-              o.z = pack_bf16(activate<EPI>(v[8 * j + 4]), activate<EPI>(v[8 * j + 5]));
-              o.w = pack_bf16(activate<EPI>(v[8 * j + 6]), activate<EPI>(v[8 * j + 7]));
-              op[j] = o;
-            }
+          for (int j = 0; j < CH / 4; ++j) {
+            const float4 b = __ldg(bp + j);
+            r[4 * j] = __float_as_uint(__uint_as_float(r[4 * j]) + b.x);
+            r[4 * j + 1] = __float_as_uint(__uint_as_float(r[4 * j + 1]) + b.y);
+            r[4 * j + 2] = __float_as_uint(__uint_as_float(r[4 * j + 2]) + b.z);
+            r[4 * j + 3] = __float_as_uint(__uint_as_float(r[4 * j + 3]) + b.w);
           }
         }
+        if (kF32Out) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<uint4*>(dst + (((uint32_t)j ^ sw) << 4)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            uint4 o;
+            o.x = pack_bf16(activate<EPI>(__uint_as_float(r[8 * j + 0])), activate<EPI>(__uint_as_float(r[8 * j + 1])));
+            o.y = pack_bf16(activate<EPI>(__uint_as_float(r[8 * j + 2])), activate<EPI>(__uint_as_float(r[8 * j + 3])));
+            o.z = pack_bf16(activate<EPI>(__uint_as_float(r[8 * j + 4])), activate<EPI>(__uint_as_float(r[8 * j + 5])));
+            o.w = pack_bf16(activate<EPI>(__uint_as_float(r[8 * j + 6])), activate<EPI>(__uint_as_float(r[8 * j + 7])));
+            *reinterpret_cast<uint4*>(dst + (((uint32_t)j ^ sw) << 4)) = o;
+          }
+        }
+        ptx::fence_proxy_async();                      // generic-proxy smem writes -> visible to the TMA unit
+        __syncwarp();
+        if (lane == 0) {
+          if (EPI == EPI_RESIDUAL_F32) ptx::tma_reduce_add_2d(&tmap_out, my_stage + buf * 4096, n0 + c0, row0);
+          else ptx::tma_store_2d(&tmap_out, my_stage + buf * 4096, n0 + c0, row0);
+          ptx::bulk_commit_group();
+        }
+        buf ^= 1;
       }
-      ptx::tcgen05_fence_before();
-      ptx::mbar_arrive(tmem_empty + acc);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (lane == 0) ptx::bulk_wait_group<0>();          // all stores / reductions complete before exit
   }
 
   ptx::tcgen05_fence_before();
@@ -206,24 +221,26 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-// 2-D bf16 row-major [rows, cols] tensor, box = {BK columns, box_rows rows}, 128-byte swizzle
-int make_tmap_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+// 2-D row-major [rows, cols] tensor, box = {box_cols, box_rows} with box_cols * elem = 128 B, 128-byte swizzle
+static int make_tmap(CUtensorMap* map, const void* ptr, bool f32, uint64_t rows, uint64_t cols, uint32_t box_cols,
+                     uint32_t box_rows) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) { set_error("cuTensorMapEncodeTiled entry point not available"); return EGPT_ERR_CUDA; }
+  const uint64_t esz = f32 ? 4 : 2;
   cuuint64_t dims[2] = {cols, rows};
-  cuuint64_t strides[1] = {cols * 2};
-  cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
+  cuuint64_t strides[1] = {cols * esz};
+  cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = fn(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                  const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return EGPT_ERR_CUDA; }
   return EGPT_OK;
 }
 
 template <int EPI>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const float* bias, void* out, long long M, int N,
-                       int K, cudaStream_t stream) {
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const float* bias,
+                       long long M, int N, int K, cudaStream_t stream) {
   static std::once_flag once;   // attribute is per function; one process drives one device
   cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [&] {
@@ -232,7 +249,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const float
   EGPT_CUDA(attr_err);
   const long long tiles = ((M + BM - 1) / BM) * (N / BN);
   const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
-  gemm_bf16_kernel<EPI><<<grid, kGemmThreads, kGemmSmem, stream>>>(ta, tb, bias, out, M, N, K);
+  gemm_bf16_kernel<EPI><<<grid, kGemmThreads, kGemmSmem, stream>>>(ta, tb, to, bias, M, N, K);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
 }
@@ -246,14 +263,17 @@ int gemm_bf16(const void* A, const void* B, const float* bias, void* out, long l
                  (bias == nullptr || (uintptr_t)bias % 16 == 0), "gemm: pointers must be 16-byte aligned");
   CUtensorMap ta, tb;
   ProfScope prof(PROF_GEMM, 2.0 * (double)M * N * K, stream);
-  EGPT_TRY(make_tmap_bf16(&ta, A, (uint64_t)M, (uint64_t)K, BM));
-  EGPT_TRY(make_tmap_bf16(&tb, B, (uint64_t)N, (uint64_t)K, BN));
+  CUtensorMap to;
+  const bool f32_out = epilogue == EPI_RESIDUAL_F32 || epilogue == EPI_STORE_F32;
+  EGPT_TRY(make_tmap(&ta, A, false, (uint64_t)M, (uint64_t)K, BK, BM));
+  EGPT_TRY(make_tmap(&tb, B, false, (uint64_t)N, (uint64_t)K, BK, BN));
+  EGPT_TRY(make_tmap(&to, out, f32_out, (uint64_t)M, (uint64_t)N, f32_out ? 32 : 64, 32));
   switch (epilogue) {
-    case EPI_BIAS_BF16: return launch_gemm<EPI_BIAS_BF16>(ta, tb, bias, out, M, N, K, stream);
-    case EPI_QUICKGELU_BF16: return launch_gemm<EPI_QUICKGELU_BF16>(ta, tb, bias, out, M, N, K, stream);
-    case EPI_GELU_BF16: return launch_gemm<EPI_GELU_BF16>(ta, tb, bias, out, M, N, K, stream);
-    case EPI_RESIDUAL_F32: return launch_gemm<EPI_RESIDUAL_F32>(ta, tb, bias, out, M, N, K, stream);
-    case EPI_STORE_F32: return launch_gemm<EPI_STORE_F32>(ta, tb, bias, out, M, N, K, stream);
+    case EPI_BIAS_BF16: return launch_gemm<EPI_BIAS_BF16>(ta, tb, to, bias, M, N, K, stream);
+    case EPI_QUICKGELU_BF16: return launch_gemm<EPI_QUICKGELU_BF16>(ta, tb, to, bias, M, N, K, stream);
+    case EPI_GELU_BF16: return launch_gemm<EPI_GELU_BF16>(ta, tb, to, bias, M, N, K, stream);
+    case EPI_RESIDUAL_F32: return launch_gemm<EPI_RESIDUAL_F32>(ta, tb, to, bias, M, N, K, stream);
+    case EPI_STORE_F32: return launch_gemm<EPI_STORE_F32>(ta, tb, to, bias, M, N, K, stream);
   }
   set_error("gemm: unknown epilogue %d", epilogue);
   return EGPT_ERR_INVALID;

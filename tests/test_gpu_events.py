@@ -215,18 +215,15 @@ def test_split_dsec_window_and_large_sorted_stream(dev):
     from eventgpt_b200 import common
     from oracle import events as oev
     ev, _, _ = load_golden_events("dsec_000069")       # int64 absolute microseconds
-    for dt in (50000, 10000, 7):
+    for dt in (50000, 10000):
         got = common.split_event_by_time(ev, dt)
-        want = oev.split_event_by_time(ev, dt) if dt > 7 else None
-        if want is None:
-            with pytest.raises(ValueError):
-                pass
-                raise ValueError
-            continue
+        want = oev.split_event_by_time(ev, dt)
         assert len(got) == len(want)
         for g, w in zip(got, want):
             for k in "xytp":
                 assert np.array_equal(g[k], w[k])
+    with pytest.raises(ValueError):       # 50 ms / 7 us = 7143 bins > max_windows: reported, not silently truncated
+        common.split_event_by_time(ev, 7, max_windows=4096)
     rng = np.random.default_rng(9)
     n = 3_000_000
     st = dict(t=np.sort(rng.integers(0, 1_000_000, n)).astype(np.int64), x=rng.integers(0, 640, n).astype(np.uint16),
