@@ -58,6 +58,8 @@ SIGNATURES = {
     "egpt_raster_frame_stride": (_sz, [_i, _i]),
     "egpt_raster_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "egpt_raster": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "egpt_raster_static_max_keys": (_i64, []),
+    "egpt_raster_static": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "egpt_preprocess_workspace_bytes": (_sz, [_i, _i]),
     "egpt_preprocess": (_i, [_vp, _sz, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "egpt_create": (_i, [C.POINTER(Weights), _i, C.POINTER(_vp)]),

@@ -12,6 +12,7 @@
 // enough to stay resident in the 126 MB L2, so DRAM traffic stays at the
 // algorithmic 5 B/event read + 3 B/pixel written.
 #include "common.cuh"
+#include <mutex>
 
 namespace egpt {
 
@@ -496,4 +497,63 @@ extern "C" int egpt_split_time(const void* x, const void* y, const void* t, cons
       t_dtype, dtype_size(p_dtype), pl, interval, minmax, table, out_x, out_y, out_t, out_p);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
+}
+
+
+// ------------------------------------------------------------------------------------------
+// egpt_raster_static: rasterisation for callers that cannot allocate device memory.
+// ------------------------------------------------------------------------------------------
+// Same result as egpt_raster, but the key planes live in a fixed array that is part of the
+// library image instead of a caller-supplied workspace.  Capacity: kStaticMaxKeys keys
+// (n_windows * n_frames * H * W), i.e. one 5-frame window of a 1280x720 sensor, or three
+// 5-frame windows of a 640x480 one.  Every GPU that loads the library carries these 17.6 MiB
+// until the process exits.
+namespace egpt {
+constexpr long long kStaticMaxKeys = 5LL * 720 * 1280;
+constexpr long long kStaticSlackWords = 1024;   // egpt_raster rounds its workspace need up by < 2 KiB
+static __device__ __align__(256) uint32_t g_static_key_planes[kStaticMaxKeys + kStaticSlackWords];
+
+// The array's name is only a handle on the host; the device address has to be asked for, once per
+// device, while that device is current.
+static std::mutex g_static_mu;
+static void* g_static_ptr[64] = {nullptr};
+static int static_scratch_address(void** out) {
+  int dev = -1;
+  EGPT_CUDA(cudaGetDevice(&dev));
+  EGPT_CHECK_ARG(dev >= 0 && dev < 64, "egpt_raster_static: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (g_static_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_key_planes);
+    if (e != cudaSuccess || ptr == nullptr) {
+      set_error("egpt_raster_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return EGPT_ERR_CUDA;
+    }
+    g_static_ptr[dev] = ptr;
+  }
+  *out = g_static_ptr[dev];
+  return EGPT_OK;
+}
+}  // namespace egpt
+
+extern "C" int64_t egpt_raster_static_max_keys(void) { return egpt::kStaticMaxKeys; }
+
+extern "C" int egpt_raster_static(const void* x, const void* y, const void* p, int x_dtype, int y_dtype, int p_dtype,
+                                  const int64_t* window_offsets, int n_windows, int n_frames, int mode, int H, int W,
+                                  int fixed_canvas, uint8_t* out_frames, int32_t* out_hw, int32_t* status,
+                                  void* stream) {
+  EGPT_CHECK_ARG(n_windows > 0 && n_frames > 0 && H > 0 && W > 0, "egpt_raster_static: bad shape %d x %d x %d x %d",
+                 n_windows, n_frames, H, W);
+  const long long keys = (long long)n_windows * n_frames * H * W;
+  if (keys > kStaticMaxKeys) {
+    set_error("egpt_raster_static: %d windows x %d frames x %dx%d needs %lld key cells, the built-in scratch holds %lld "
+              "(use egpt_raster with a caller workspace for larger requests)", n_windows, n_frames, H, W, keys, kStaticMaxKeys);
+    return EGPT_ERR_TOO_LARGE;
+  }
+  void* scratch = nullptr;
+  EGPT_TRY(static_scratch_address(&scratch));
+  // egpt_raster zeroes the planes it is about to use, so whatever the previous call left behind is harmless
+  return egpt_raster(x, y, p, x_dtype, y_dtype, p_dtype, window_offsets, n_windows, n_frames, mode, H, W, fixed_canvas,
+                     out_frames, out_hw, nullptr, status, scratch,
+                     (size_t)(kStaticMaxKeys + kStaticSlackWords) * sizeof(uint32_t), stream);
 }

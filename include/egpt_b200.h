@@ -102,6 +102,28 @@ int egpt_raster(const void* x, const void* y, const void* p, int x_dtype, int y_
                 uint8_t* out_frames, int32_t* out_hw, int32_t* out_counts,
                 int32_t* status, void* workspace, size_t workspace_bytes, void* stream);
 
+/* egpt_raster_static -- no counterpart in the reference.  The same rasterisation for callers   */
+/* that are not allowed to create device memory: a sensor-acquisition or plug-in thread that    */
+/* was handed its input and output buffers by the host application and must not call cudaMalloc */
+/* (it would stall the device the application is sharing, and it can fail at a moment the       */
+/* thread has no way to recover from).  The key planes that egpt_raster keeps in a caller       */
+/* workspace live here in a fixed array inside the library, so the call allocates nothing and   */
+/* takes no workspace argument.  Limits and rules:                                              */
+/*   - n_windows * n_frames * H * W <= egpt_raster_static_max_keys() (= 5*720*1280: one 5-frame */
+/*     window at 1280x720, or three at 640x480); larger requests return EGPT_ERR_TOO_LARGE.     */
+/*     Every GPU that loads the library holds this 17.6 MiB array until the process exits.      */
+/*   - the first call on a device looks up the array's device address (with that device         */
+/*     current); make that first call before starting any stream capture.                       */
+/*   - all calls on a device share the one array: two calls that may overlap on the GPU         */
+/*     (different streams, different threads) race -- serialise them.  The array keeps the last */
+/*     call's keys; each call clears the part it uses before rasterising.                       */
+/*   - per-pixel counts are not offered here; everything else is as in egpt_raster.             */
+int64_t egpt_raster_static_max_keys(void);
+int egpt_raster_static(const void* x, const void* y, const void* p, int x_dtype, int y_dtype, int p_dtype,
+                       const int64_t* window_offsets, int n_windows, int n_frames,
+                       int mode, int H, int W, int fixed_canvas,
+                       uint8_t* out_frames, int32_t* out_hw, int32_t* status, void* stream);
+
 /* ------------------------------------------------------------------------------------------ */
 /* a-5  event_processor(img)['pixel_values'][0].to(bf16)         common/common.py:124-127       */
 /* CLIPImageProcessor: resize shortest edge -> 336 with Pillow's antialiased bicubic (8-bit     */
