@@ -188,6 +188,12 @@ int attention(const void* qkv, int n_frames_total, void* out, cudaStream_t strea
 
 }  // namespace egpt
 
+namespace egpt { int attention_tc(const void* qkv, int n_frames_total, void* out, cudaStream_t stream); }
+
 extern "C" int egpt_attention(const uint16_t* qkv, int n_frames_total, uint16_t* out, void* stream) {
+  return egpt::attention_tc(qkv, n_frames_total, out, (cudaStream_t)stream);
+}
+// bring-up comparator (tests only): the mma.sync kernel
+extern "C" int egpt_attention_legacy(const uint16_t* qkv, int n_frames_total, uint16_t* out, void* stream) {
   return egpt::attention(qkv, n_frames_total, out, (cudaStream_t)stream);
 }

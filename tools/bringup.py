@@ -124,25 +124,39 @@ def stage_gemm():
 
 
 def stage_attn():
+    import ctypes as C
     import torch
     from eventgpt_b200 import events as E
     from eventgpt_b200._lib import lib, check
     dev = torch.device("cuda:0")
     torch.manual_seed(0)
-    F = 3
-    qkv = (torch.randn(F * 577, 3072, device=dev)).bfloat16()
-    out = torch.empty(F * 577, 1024, device=dev, dtype=torch.bfloat16)
-    check(lib().egpt_attention(E.ptr(qkv), F, E.ptr(out), E.stream_ptr(dev)), "attn")
-    torch.cuda.synchronize()
-    q, k, v = (qkv.float().view(F, 577, 3, 16, 64)[:, :, i].transpose(1, 2) for i in range(3))
-    ref = (torch.softmax(q @ k.transpose(-1, -2), -1) @ v).transpose(1, 2).reshape(F * 577, 1024)
-    err = (out.float() - ref).abs().max().item()
-    print(f"attention F={F}: max-abs {err:.4g} {'OK' if err < 3e-2 else 'BAD'}")
+    fns = {"tcgen05": lib().egpt_attention}
+    if hasattr(lib(), "egpt_attention_legacy"):
+        leg = lib().egpt_attention_legacy
+        leg.restype, leg.argtypes = C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        fns["legacy"] = leg
+    for F in (1, 3):
+        qkv = (torch.randn(F * 577, 3072, device=dev)).bfloat16()
+        q, k, v = (qkv.float().view(F, 577, 3, 16, 64)[:, :, i].transpose(1, 2) for i in range(3))
+        ref = (torch.softmax(q @ k.transpose(-1, -2), -1) @ v).transpose(1, 2).reshape(F * 577, 1024)
+        for name, fn in fns.items():
+            out = torch.full((F * 577, 1024), float("nan"), device=dev, dtype=torch.bfloat16)
+            check(fn(E.ptr(qkv), F, E.ptr(out), E.stream_ptr(dev)), "attn")
+            torch.cuda.synchronize()
+            d = (out.float() - ref).abs()
+            err = d.max().item()
+            print(f"attention[{name}] F={F}: max-abs {err:.4g} nan {int(torch.isnan(out.float()).sum())} {'OK' if err < 3e-2 else 'BAD'}")
+            if not err < 3e-2:
+                dd = d.view(F, 577, 16, 64)
+                print("   err by head", [round(x, 3) for x in dd.amax(dim=(0, 1, 3)).tolist()])
+                print("   err by row/64", [round(x, 3) for x in dd[0].amax(dim=(1, 2)).view(-1)[:576].view(9, 64).amax(1).tolist()], round(dd[0, 576].max().item(), 3))
+                print("   err by dim/8", [round(x, 3) for x in dd.amax(dim=(0, 1, 2)).view(8, 8).amax(1).tolist()])
     F = 160
     qkv = (torch.randn(F * 577, 3072, device=dev) * 0.5).bfloat16()
     out = torch.empty(F * 577, 1024, device=dev, dtype=torch.bfloat16)
-    ms = cuda_time(lambda: check(lib().egpt_attention(E.ptr(qkv), F, E.ptr(out), E.stream_ptr(dev))))
-    print(f"attention F=160: {ms:.3f} ms  {4*577*577*64*16*F/ms/1e9:.0f} TFLOP/s")
+    for name, fn in fns.items():
+        ms = cuda_time(lambda: check(fn(E.ptr(qkv), F, E.ptr(out), E.stream_ptr(dev))))
+        print(f"attention[{name}] F=160: {ms:.3f} ms  {4*577*577*64*16*F/ms/1e9:.0f} TFLOP/s")
 
 
 def stage_misc():
