@@ -123,8 +123,9 @@ struct Bars {
 
 __global__ void __launch_bounds__(kThreads, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_tail,
-                    __nv_bfloat16* __restrict__ out) {
+                    __nv_bfloat16* __restrict__ out, long long* __restrict__ trace) {
   extern __shared__ uint8_t smem_raw[];
+#define TR(slot) do { if (trace != nullptr && blockIdx.x == 0) trace[(slot)] = clock64(); } while (0)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   Bars* bars = reinterpret_cast<Bars*>(smem + kSmemBar);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -148,7 +149,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
   __syncthreads();
   ptx::tcgen05_fence_after();
   const uint32_t tmem_base = bars->tmem_ptr;
-
+  // hand registers from the four control warps to the softmax warps (the row block lives in registers)
+  if (warp < 4) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
   if (warp == 0 && lane == 0) {
     // ===== TMA producer =====
     // Q tile 0 first, then K and V block by block (64-row boxes) so the first MMAs can start early
@@ -181,45 +184,54 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
     // ===== MMA issuer =====
     const uint32_t sK = ptx::smem_u32(smem + kSmemK), sV = ptx::smem_u32(smem + kSmemV);
     const uint32_t sQ = ptx::smem_u32(smem + kSmemQ);
+    const uint64_t dV0 = make_desc_mn_sw128(sV), dK0 = ptx::make_smem_desc_sw128(sK), dQ = ptx::make_smem_desc_sw128(sQ);
     auto issue_pv = [&](int g) {
       const int j = g & 3, b = g & 1, n = g >> 1;
       if (g < kBlocks) ptx::mbar_wait(&bars->v_full[j], 0);
+      if (g < 12) TR(256 + g * 8 + 2);
       ptx::mbar_wait(&bars->p_full[b], (uint32_t)(n & 1));
+      if (g < 12) TR(256 + g * 8 + 3);
       ptx::mbar_wait(&bars->o_empty[b], (uint32_t)((n & 1) ^ 1));
       ptx::tcgen05_fence_after();
-      const uint32_t idesc = idesc_bf16(kQTile, kD, 1);
+      constexpr uint32_t idesc = idesc_bf16(kQTile, kD, 1);
       const uint32_t tmem_o = tmem_base + kTmemO + (uint32_t)(b * kD);
       const uint32_t tmem_p = tmem_base + kTmemS + (uint32_t)(b * kBlk);
-      const int ksteps = block_cols(j) / 16;
-      for (int kk = 0; kk < ksteps; ++kk) {
-        // A = P from TMEM: 16 keys = 8 packed columns per k-step; B = V rows j*192 + 16*kk .. +15
-        const uint64_t db = make_desc_mn_sw128(sV + (uint32_t)((j * kBlk + kk * 16) * kRowBytes));
-        umma_bf16_ts(tmem_o, tmem_p + (uint32_t)(kk * 8), db, idesc, kk != 0);
+      // A = P from TMEM: 16 keys = 8 packed columns per k-step; B = V rows j*192 + 16*kk .. +15 (2048 B = 128 desc units)
+      const uint64_t db0 = dV0 + (uint64_t)(j * (kBlk * kRowBytes >> 4));
+      if (j < 3) {
+#pragma unroll
+        for (int kk = 0; kk < kBlk / 16; ++kk)
+          umma_bf16_ts(tmem_o, tmem_p + (uint32_t)(kk * 8), db0 + (uint64_t)(kk * 128), idesc, kk != 0);
+      } else {
+        umma_bf16_ts(tmem_o, tmem_p, db0, idesc, 0u);
       }
       ptx::umma_commit(&bars->o_full[b]);
+      if (g < 12) TR(256 + g * 8 + 4);
     };
     for (int t = 0; t < kQTiles; ++t) {
       ptx::mbar_wait(&bars->q_full, (uint32_t)(t & 1));
       for (int j = 0; j < kBlocks; ++j) {
         const int g = t * kBlocks + j, b = g & 1;
+        if (g < 12) TR(256 + g * 8 + 0);
         if (t == 0) ptx::mbar_wait(&bars->k_full[j], 0);
         // S_g overwrites the buffer that held S_{g-2} / P_{g-2}: the tensor pipe runs MMAs in issue order,
         // and P V of block g-2 was issued before this point, so no barrier is needed for that reuse.
         ptx::tcgen05_fence_after();
-        const int ncols = block_cols(j);
-        const uint32_t idesc = idesc_bf16(kQTile, ncols, 0);
+        const uint32_t idesc = j < 3 ? idesc_bf16(kQTile, kBlk, 0) : idesc_bf16(kQTile, kTail, 0);
         const uint32_t tmem_s = tmem_base + kTmemS + (uint32_t)(b * kBlk);
-        const uint64_t da = ptx::make_smem_desc_sw128(sQ);
-        const uint64_t db = ptx::make_smem_desc_sw128(sK + (uint32_t)(j * kBlk * kRowBytes));
+        const uint64_t db = dK0 + (uint64_t)(j * (kBlk * kRowBytes >> 4));
 #pragma unroll
-        for (int k = 0; k < kD / 16; ++k) ptx::umma_bf16_ss(tmem_s, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, k != 0);
+        for (int k = 0; k < kD / 16; ++k) ptx::umma_bf16_ss(tmem_s, dQ + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, k != 0);
         ptx::umma_commit(&bars->s_full[b]);
+        if (g < 12) TR(256 + g * 8 + 1);
         if (j == kBlocks - 1) ptx::umma_commit(&bars->q_empty);
         if (g >= 1) issue_pv(g - 1);
       }
     }
     issue_pv(kQTiles * kBlocks - 1);
-  } else if (warp >= 4) {
+  }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
     // ===== softmax: thread (row r, half hf) owns key columns [hf*96, hf*96+96) of a 192-key block
     // (the 16-key tail block belongs to half 0) and output dims [hf*32, hf*32+32) =====
     const int q = warp & 3, hf = (warp - 4) >> 2;
@@ -240,8 +252,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
         // number of valid (un-masked) columns among this thread's columns, and where they start
         const int col0 = j < 3 ? hf * 96 : 0;
         const int nvalid = j < 3 ? 96 : (hf == 0 ? kS - 3 * kBlk : 0);         // 96 / 1 / 0
+        const bool trc = (warp == 4 && lane == 0 && g < 12);
+        if (trc) TR(g * 16 + 0);
         ptx::mbar_wait(&bars->s_full[b], (uint32_t)(n & 1));
         ptx::tcgen05_fence_after();
+        if (trc) TR(g * 16 + 1);
         uint32_t v[3][32];
         if (j < 3) {
           ptx::tmem_ld_32x32b_x32(ts + (uint32_t)col0, v[0]);
@@ -251,6 +266,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
           tmem_ld_32x32b_x16(ts, v[0]);
         }
         ptx::tmem_ld_wait();
+        if (trc) TR(g * 16 + 2);
         float mx = -INFINITY;
         if (j < 3) {
           float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
@@ -268,6 +284,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
         mx = fmaxf(mx, xmax[(b * 2 + (hf ^ 1)) * 128 + r]);
         const float m_new = fmaxf(m, mx * kLog2e);                     // exp2 domain; finite
         const float alpha = ex2(m - m_new);                            // 0 on the first block (m = -inf)
+        if (trc) TR(g * 16 + 3);
         float s4[4] = {0.f, 0.f, 0.f, 0.f};
         // P_j (bf16 pairs) goes to columns [hf*48, hf*48+48) of the S_j buffer
         const uint32_t tp = ts + (uint32_t)(hf * 48);
@@ -295,14 +312,17 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
         }
         const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
         (void)nvalid; (void)col0;
+        if (trc) TR(g * 16 + 4);
         tmem_st_wait();
         ptx::tcgen05_fence_before();
         ptx::mbar_arrive(&bars->p_full[b]);
+        if (trc) TR(g * 16 + 5);
         // fold in the previous block's O (same max frame), then move to the new frame
         if (j >= 1) {
           const int gp = g - 1, bp = gp & 1, np = gp >> 1;
           ptx::mbar_wait(&bars->o_full[bp], (uint32_t)(np & 1));
           ptx::tcgen05_fence_after();
+          if (trc) TR(g * 16 + 6);
           uint32_t vo[32];
           ptx::tmem_ld_32x32b_x32(tmem_base + lane_base + kTmemO + (uint32_t)(bp * kD + hf * 32), vo);
           ptx::tmem_ld_wait();
@@ -315,6 +335,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
         for (int i = 0; i < 32; ++i) o[i] *= alpha;
         l = l * alpha + sum;
         m = m_new;
+        if (trc) TR(g * 16 + 7);
       }
       // last block of the tile: fold its O, combine the two halves' row sums, normalise and store
       {
@@ -368,7 +389,11 @@ static EncodeTiledFn encode_fn() {
 }
 }  // namespace at5
 
-int attention_tc(const void* qkv, int n_frames_total, void* out, cudaStream_t stream) {
+int attention_impl(const void* qkv, int n_frames_total, void* out, cudaStream_t stream, long long* trace);
+int attention(const void* qkv, int n_frames_total, void* out, cudaStream_t stream) {
+  return attention_impl(qkv, n_frames_total, out, stream, nullptr);
+}
+int attention_impl(const void* qkv, int n_frames_total, void* out, cudaStream_t stream, long long* trace) {
   using namespace at5;
   EGPT_CHECK_ARG(qkv && out && n_frames_total > 0, "attention: bad arguments");
   EGPT_CHECK_ARG(((uintptr_t)qkv % 16 == 0) && ((uintptr_t)out % 16 == 0), "attention: pointers must be 16-byte aligned");
@@ -397,9 +422,18 @@ int attention_tc(const void* qkv, int n_frames_total, void* out, cudaStream_t st
   });
   EGPT_CUDA(attr_err);
   ProfScope prof(PROF_ATTN, 4.0 * kS * kS * kD * kHeads * (double)n_frames_total, stream);
-  attention_tc_kernel<<<n_frames_total * kHeads, kThreads, kSmemTotal, stream>>>(tm, tm_tail, reinterpret_cast<__nv_bfloat16*>(out));
+  attention_tc_kernel<<<n_frames_total * kHeads, kThreads, kSmemTotal, stream>>>(tm, tm_tail, reinterpret_cast<__nv_bfloat16*>(out), trace);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
 }
 
 }  // namespace egpt
+
+// developer aid: clock64 timestamps of CTA 0's phases (softmax warp 4 lane 0: slots g*16+k; MMA thread: 256+g*8+k)
+extern "C" int egpt_attention_trace(const uint16_t* qkv, int n_frames_total, uint16_t* out, long long* trace, void* stream) {
+  return egpt::attention_impl(qkv, n_frames_total, out, (cudaStream_t)stream, trace);
+}
+
+extern "C" int egpt_attention(const uint16_t* qkv, int n_frames_total, uint16_t* out, void* stream) {
+  return egpt::attention(qkv, n_frames_total, out, (cudaStream_t)stream);
+}
