@@ -73,6 +73,19 @@ __device__ __forceinline__ float ex2(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// 2^x for x <= 0 on the FMA/ALU pipes (Cody-Waite split + cubic), used for a quarter of the
+// elements so the MUFU pipe (16 exp2/clk/SM, the unit this kernel saturates) is not the only
+// exponential engine.  Relative error < 1e-4, far below the bf16 rounding P undergoes anyway.
+__device__ __forceinline__ float ex2_poly(float x) {
+  x = fmaxf(x, -126.0f);
+  const float t = x + 12582912.0f;                 // 1.5 * 2^23: rounds x to the nearest integer n
+  const float n = t - 12582912.0f;
+  const float f = x - n;                           // [-0.5, 0.5]
+  float p = fmaf(f, 0.0555041f, 0.2402265f);
+  p = fmaf(p, f, 0.6931472f);
+  p = fmaf(p, f, 1.0f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
@@ -125,7 +138,11 @@ __global__ void __launch_bounds__(kThreads, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_tail,
                     __nv_bfloat16* __restrict__ out, long long* __restrict__ trace) {
   extern __shared__ uint8_t smem_raw[];
+#ifdef EGPT_ATTN_TRACE   // developer aid: clock64 phase stamps of CTA 0 (tools/attn_trace.py)
 #define TR(slot) do { if (trace != nullptr && blockIdx.x == 0) trace[(slot)] = clock64(); } while (0)
+#else
+#define TR(slot) do { } while (0)
+#endif
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   Bars* bars = reinterpret_cast<Bars*>(smem + kSmemBar);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -295,7 +312,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
               const float p0 = ex2(fmaf(__uint_as_float(v[c][2 * i]), kLog2e, -m_new));
-              const float p1 = ex2(fmaf(__uint_as_float(v[c][2 * i + 1]), kLog2e, -m_new));
+              const float x1 = fmaf(__uint_as_float(v[c][2 * i + 1]), kLog2e, -m_new);
+              const float p1 = (i & 1) ? ex2_poly(x1) : ex2(x1);
               s4[i & 3] += p0 + p1;
               w[i] = pack2(p0, p1);
             }

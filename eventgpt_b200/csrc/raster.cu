@@ -71,45 +71,62 @@ raster_scatter_kernel(const void* __restrict__ xv, const void* __restrict__ yv, 
   }
 
   if (FAST) {
-    const long long g0 = sl.start >> 3, g1 = (sl.end + 7) >> 3;   // groups of 8 events
-    for (long long g = g0 + (long long)blockIdx.x * kScatterThreads + threadIdx.x; g < g1;
-         g += (long long)gridDim.x * kScatterThreads) {
-      const long long base = g << 3;
-      unsigned xw[4], yw[4], pw[2];
-      if (base >= sl.start && base + 8 <= sl.end) {
-        const uint4 xs = __ldg(reinterpret_cast<const uint4*>(xv) + g);
-        const uint4 ys = __ldg(reinterpret_cast<const uint4*>(yv) + g);
-        const uint2 ps = __ldg(reinterpret_cast<const uint2*>(pv) + g);
-        xw[0] = xs.x; xw[1] = xs.y; xw[2] = xs.z; xw[3] = xs.w;
-        yw[0] = ys.x; yw[1] = ys.y; yw[2] = ys.z; yw[3] = ys.w;
-        pw[0] = ps.x; pw[1] = ps.y;
-      } else {
-        // boundary group: element loads, never outside [start, end)
-        xw[0] = xw[1] = xw[2] = xw[3] = yw[0] = yw[1] = yw[2] = yw[3] = pw[0] = pw[1] = 0;
+    // groups of 8 events; every thread takes kUnroll groups per trip with all its loads issued first
+    // (the kernel is bound by load latency, not by the L2 reductions)
+    constexpr int kUnroll = 4;
+    const long long g0 = sl.start >> 3, g1 = (sl.end + 7) >> 3;
+    const long long stride = (long long)gridDim.x * kScatterThreads;
+    for (long long gb = g0 + (long long)blockIdx.x * kScatterThreads + threadIdx.x; gb < g1; gb += stride * kUnroll) {
+      uint4 xs[kUnroll], ys[kUnroll];
+      uint2 ps[kUnroll];
+      bool whole[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long g = gb + u * stride, base = g << 3;
+        whole[u] = g < g1 && base >= sl.start && base + 8 <= sl.end;
+        if (whole[u]) {
+          xs[u] = __ldg(reinterpret_cast<const uint4*>(xv) + g);
+          ys[u] = __ldg(reinterpret_cast<const uint4*>(yv) + g);
+          ps[u] = __ldg(reinterpret_cast<const uint2*>(pv) + g);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long g = gb + u * stride, base = g << 3;
+        if (g >= g1) break;
+        unsigned xw[4], yw[4], pw[2];
+        if (whole[u]) {
+          xw[0] = xs[u].x; xw[1] = xs[u].y; xw[2] = xs[u].z; xw[3] = xs[u].w;
+          yw[0] = ys[u].x; yw[1] = ys[u].y; yw[2] = ys[u].z; yw[3] = ys[u].w;
+          pw[0] = ps[u].x; pw[1] = ps[u].y;
+        } else {
+          // boundary group: element loads, never outside [start, end)
+          xw[0] = xw[1] = xw[2] = xw[3] = yw[0] = yw[1] = yw[2] = yw[3] = pw[0] = pw[1] = 0;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const long long i = base + j;
+            if (i < sl.start || i >= sl.end) continue;
+            xw[j >> 1] |= (unsigned)((const uint16_t*)xv)[i] << ((j & 1) * 16);
+            yw[j >> 1] |= (unsigned)((const uint16_t*)yv)[i] << ((j & 1) * 16);
+            pw[j >> 2] |= (unsigned)((const uint8_t*)pv)[i] << ((j & 3) * 8);
+          }
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const long long i = base + j;
           if (i < sl.start || i >= sl.end) continue;
-          xw[j >> 1] |= (unsigned)((const uint16_t*)xv)[i] << ((j & 1) * 16);
-          yw[j >> 1] |= (unsigned)((const uint16_t*)yv)[i] << ((j & 1) * 16);
-          pw[j >> 2] |= (unsigned)((const uint8_t*)pv)[i] << ((j & 3) * 8);
-        }
-      }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const long long i = base + j;
-        if (i < sl.start || i >= sl.end) continue;
-        const unsigned x = (xw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-        const unsigned y = (yw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-        const unsigned p = (pw[j >> 2] >> ((j & 3) * 8)) & 0xffu;
-        any = true;
-        if (mode == EGPT_RASTER_LAST_WINS) {
-          emit_event(x, y, p == 0, (unsigned)(i - sl.start + 1) << 1, mode, H, W, plane, counts, mx, my, flags);
-        } else {
-          if (x >= (unsigned)W || y >= (unsigned)H) { flags |= EGPT_FLAG_OUT_OF_RANGE; continue; }
-          mx = max(mx, x); my = max(my, y);
-          if (p == 0) atomicMax(plane + y * (unsigned)W + x, 2u);
-          else if (p == 1) atomicMax(plane + y * (unsigned)W + x, 1u);
+          const unsigned x = (xw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
+          const unsigned y = (yw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
+          const unsigned p = (pw[j >> 2] >> ((j & 3) * 8)) & 0xffu;
+          any = true;
+          if (mode == EGPT_RASTER_LAST_WINS) {
+            emit_event(x, y, p == 0, (unsigned)(i - sl.start + 1) << 1, mode, H, W, plane, counts, mx, my, flags);
+          } else {
+            if (x >= (unsigned)W || y >= (unsigned)H) { flags |= EGPT_FLAG_OUT_OF_RANGE; continue; }
+            mx = max(mx, x); my = max(my, y);
+            if (p == 0) atomicMax(plane + y * (unsigned)W + x, 2u);
+            else if (p == 1) atomicMax(plane + y * (unsigned)W + x, 1u);
+          }
         }
       }
     }
