@@ -205,6 +205,24 @@ __global__ void pool_finish_kernel(const float* __restrict__ partial, int chunks
   else *reinterpret_cast<float*>(o) = v;
 }
 
+// ---- multimodal splice gather (model/EventChatModel.py:355-465) -----------------------------------
+// out[row, :] = embed_table[src[row]] (src >= 0), zero (src == -1, right padding), or
+// event_features row -(src + 2) (src <= -2; rows of the [NF*T, C] feature matrix).  16-byte vectors.
+__global__ void __launch_bounds__(256)
+splice_gather_kernel(const uint4* __restrict__ table, const uint4* __restrict__ feats, const int32_t* __restrict__ src,
+                     uint4* __restrict__ out, long long rows, int vec_per_row) {
+  const long long total = rows * vec_per_row;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / vec_per_row;
+    const int v = (int)(i - row * vec_per_row);
+    const int s = __ldg(src + row);
+    uint4 val = make_uint4(0u, 0u, 0u, 0u);
+    if (s >= 0) val = __ldg(table + (size_t)s * vec_per_row + v);
+    else if (s <= -2) val = __ldg(feats + (size_t)(-(long long)s - 2) * vec_per_row + v);
+    out[i] = val;
+  }
+}
+
 // ---- weight packing ------------------------------------------------------------------------------
 __global__ void scale_bf16_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, float scale,
                                   long long n) {
@@ -277,6 +295,22 @@ static int pool_chunks(int s) { return (s + kPoolRows - 1) / kPoolRows; }
 }  // namespace egpt
 
 using namespace egpt;
+
+extern "C" int egpt_splice_embeddings(const uint16_t* embed_table, const uint16_t* event_features, const int32_t* src,
+                                      int64_t rows, int c, uint16_t* out, void* stream_) {
+  cudaStream_t st = (cudaStream_t)stream_;
+  EGPT_CHECK_ARG(embed_table && event_features && src && out, "egpt_splice_embeddings: null pointer argument");
+  EGPT_CHECK_ARG(rows > 0 && c > 0 && c % 8 == 0, "egpt_splice_embeddings: rows=%lld c=%d (c must be a multiple of 8)", (long long)rows, c);
+  EGPT_CHECK_ARG(((uintptr_t)embed_table % 16 == 0) && ((uintptr_t)event_features % 16 == 0) && ((uintptr_t)out % 16 == 0),
+                 "egpt_splice_embeddings: pointers must be 16-byte aligned");
+  ProfScope prof(PROF_ELEMENTWISE, 2.0 * (double)rows * c * 2, st);
+  long long blocks = (rows * (c / 8) + 255) / 256;
+  if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+  splice_gather_kernel<<<(unsigned)blocks, 256, 0, st>>>((const uint4*)embed_table, (const uint4*)event_features, src,
+                                                         (uint4*)out, rows, c / 8);
+  EGPT_LAUNCH_CHECK();
+  return EGPT_OK;
+}
 
 extern "C" size_t egpt_pool_workspace_bytes(int batch, int t, int c) {
   if (batch <= 0 || t <= 0 || c <= 0) return 0;

@@ -15,6 +15,9 @@ from ._lib import lib, check
 from .weights import VT
 
 TOKENS, HID, LLM = 577, 1024, 4096
+IGNORE_INDEX = -100          # dataset/constants.py:7
+EVENT_TOKEN_INDEX = -200     # dataset/constants.py:8
+MAX_PROMPT_LEN = 2048        # model/EventChatModel.py:415
 
 
 def get_spatio_temporal_features(features, num_temporal_tokens=None):
@@ -43,6 +46,78 @@ def _pool(features, num_temporal_tokens=None):
     check(lib().egpt_spatio_temporal_pool(E.ptr(f), 1 if f.dtype == torch.float32 else 0, B, t, s, c, nt, E.ptr(out),
                                           E.ptr(ws), ws.numel(), E.stream_ptr(f.device)), "egpt_spatio_temporal_pool")
     return out
+
+
+def splice_event_features(embed_table, input_ids, position_ids, attention_mask, labels, event_features):
+    """The multimodal splice of ``prepare_inputs_labels_for_multimodal`` (model/EventChatModel.py:355-465).
+
+    ``embed_table``: the LLM's ``embed_tokens.weight`` [V, C] (bf16, GPU); ``event_features``: [NF, T, C]
+    (bf16, GPU), consumed in order -- one entry per <event> token (-200) and one per sample without any,
+    as upstream.  ``input_ids`` / ``attention_mask`` / ``labels`` / ``position_ids`` as the reference takes
+    them (CPU or GPU).  Returns (position_ids, attention_mask, inputs_embeds, labels) = elements 1, 2, 4, 5 of
+    the reference's tuple, with its ``None`` conventions.  The index bookkeeping mirrors the reference's
+    Python on the host (it is O(tokens)); the embedding gather, feature copy, truncation and right padding
+    are one kernel (egpt_splice_embeddings)."""
+    if not (embed_table.is_cuda and event_features.is_cuda):
+        raise _lib.EgptError("eventgpt_b200 has no CPU path: embed_table and event_features must live on the GPU")
+    dev = embed_table.device
+    ids_h = input_ids.detach().cpu()
+    _labels, _position_ids, _attention_mask = labels, position_ids, attention_mask
+    am_h = torch.ones_like(ids_h, dtype=torch.bool) if attention_mask is None else attention_mask.detach().cpu().bool()
+    lab_h = torch.full_like(ids_h, IGNORE_INDEX) if labels is None else labels.detach().cpu()
+    NF, T, C = event_features.shape
+    srcs, labs, cur = [], [], 0
+    for b in range(ids_h.shape[0]):
+        cur_ids = ids_h[b][am_h[b]]
+        cur_lab = lab_h[b][am_h[b]]
+        ev_pos = torch.where(cur_ids == EVENT_TOKEN_INDEX)[0].tolist()
+        if not ev_pos:                                   # :380-387 -- still consumes one feature entry
+            if cur >= NF:
+                raise IndexError(f"index {cur} is out of bounds for dimension 0 with size {NF}")
+            srcs.append(cur_ids.to(torch.int32))
+            labs.append(cur_lab)
+            cur += 1
+            continue
+        bounds = [-1] + ev_pos + [cur_ids.shape[0]]
+        s_parts, l_parts = [], []
+        for i in range(len(bounds) - 1):
+            s_parts.append(cur_ids[bounds[i] + 1: bounds[i + 1]].to(torch.int32))
+            l_parts.append(cur_lab[bounds[i] + 1: bounds[i + 1]])
+            if i < len(ev_pos):
+                if cur >= NF:
+                    raise IndexError(f"index {cur} is out of bounds for dimension 0 with size {NF}")
+                s_parts.append(-(torch.arange(cur * T, (cur + 1) * T, dtype=torch.int32) + 2))
+                l_parts.append(torch.full((T,), IGNORE_INDEX, dtype=cur_lab.dtype))
+                cur += 1
+        srcs.append(torch.cat(s_parts))
+        labs.append(torch.cat(l_parts))
+    srcs = [x[:MAX_PROMPT_LEN] for x in srcs]            # :416-418
+    labs = [x[:MAX_PROMPT_LEN] for x in labs]
+    B, max_len = len(srcs), max(x.shape[0] for x in srcs)
+    src = torch.full((B, max_len), -1, dtype=torch.int32)
+    new_labels = torch.full((B, max_len), IGNORE_INDEX, dtype=lab_h.dtype)
+    new_am = torch.zeros((B, max_len), dtype=torch.bool)
+    new_pos = torch.zeros((B, max_len), dtype=torch.long if position_ids is None else position_ids.dtype)
+    for i, (s_, l_) in enumerate(zip(srcs, labs)):
+        n = s_.shape[0]
+        src[i, :n] = s_
+        if n > 0:
+            new_labels[i, :n] = l_
+            new_am[i, :n] = True
+            new_pos[i, :n] = torch.arange(0, n, dtype=new_pos.dtype)
+    if int(src.max()) >= embed_table.shape[0]:
+        raise IndexError("index out of range in self")        # what nn.Embedding raises upstream
+    table = embed_table.to(torch.bfloat16).contiguous()
+    feats = event_features.to(torch.bfloat16).contiguous()
+    src_d = src.to(dev)
+    out = torch.empty((B, max_len, C), dtype=torch.bfloat16, device=dev)
+    check(lib().egpt_splice_embeddings(E.ptr(table), E.ptr(feats), E.ptr(src_d), B * max_len, C, E.ptr(out),
+                                       E.stream_ptr(dev)), "egpt_splice_embeddings")
+    odev = input_ids.device
+    new_labels = None if _labels is None else new_labels.to(odev)
+    new_am = None if _attention_mask is None else new_am.to(dtype=_attention_mask.dtype).to(odev)
+    new_pos = None if _position_ids is None else new_pos.to(odev)
+    return new_pos, new_am, out, new_labels
 
 
 class EventProcessor:
@@ -223,6 +298,22 @@ class EventGPTVisualFrontEnd:
         check(lib().egpt_encode_pool(self._handle, E.ptr(x), B, n, E.ptr(out), E.ptr(ws), ws.numel(),
                                      E.stream_ptr(x.device)), "egpt_encode_pool")
         return out
+
+    def prepare_inputs_labels_for_multimodal(self, embed_table, input_ids, position_ids, attention_mask, past_key_values,
+                                             labels, event_tensors=None, event_image_sizes=None, event_features=None):
+        """model/EventChatModel.py:309-465 with the LLM's embedding table passed in (this front end does not own
+        the LLM).  Same 6-tuple as upstream.  ``event_image_sizes`` is accepted and never read, as upstream."""
+        if event_tensors is None and event_features is None:
+            return input_ids, position_ids, attention_mask, past_key_values, None, labels
+        if input_ids.shape[1] == 1:
+            return input_ids, position_ids, attention_mask, past_key_values, None, labels
+        if event_features is None:
+            event_features = self.encode_events(event_tensors)
+        else:
+            # cached branch re-applies the adaptor upstream (:347-353); kept, not "fixed"
+            event_features = self.feature_adaptor(event_features)
+        pos, am, emb, lab = splice_event_features(embed_table, input_ids, position_ids, attention_mask, labels, event_features)
+        return None, pos, am, past_key_values, emb, lab
 
     # ---- fused path: events -> tokens ------------------------------------------------------------
     def visual_tokens(self, x, y, p, window_offsets, sensor_size, n_frames=E.N_FRAMES, out=None, check_flags=True):

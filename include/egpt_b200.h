@@ -201,6 +201,14 @@ int egpt_spatio_temporal_pool(const void* features, int is_f32, int batch, int t
 int egpt_encode_pool(egpt_handle* h, const uint16_t* pixel_values, int n_windows, int n_frames,
                      uint16_t* out_tokens, void* workspace, size_t workspace_bytes, void* stream);
 
+/* f-1  multimodal splice of prepare_inputs_labels_for_multimodal  model/EventChatModel.py:355-465 */
+/* One gather builds inputs_embeds [rows = B*L_out, c] (bf16): row i copies embed_table[src[i]]    */
+/* when src[i] >= 0, event_features row -(src[i]+2) of the flattened [NF*T, c] matrix when         */
+/* src[i] <= -2, and is zero (right padding) when src[i] == -1.  The host computes `src` (token    */
+/* masking, <event> positions, truncation to 2048, padding) exactly as the reference's Python does. */
+int egpt_splice_embeddings(const uint16_t* embed_table, const uint16_t* event_features, const int32_t* src,
+                           int64_t rows, int c, uint16_t* out, void* stream);
+
 /* a-3..a-9 fused: events -> tokens with no host round trip      common/common.py:110-129 +      */
 /*                                                               model/EventChatModel.py:326-343 */
 size_t egpt_visual_tokens_workspace_bytes(int n_windows, int n_frames, int H, int W);

@@ -184,5 +184,68 @@ def main():
         print(m)
 
 
+def make_splice_golden():
+    """Multimodal splice (model/EventChatModel.py:355-465) through the REAL reference: a small-vocab
+    EventChatModel with a seeded bf16-representable embedding table and an identity feature_adaptor
+    (the cached-features branch re-applies the adaptor, :347-353; identity makes that a no-op so the
+    golden pins the splice alone)."""
+    import tempfile
+    from transformers import CLIPVisionConfig, CLIPVisionModel, CLIPImageProcessor
+    from oracle import splice as osp
+    C, M = ref_harness.import_reference()
+    work = tempfile.mkdtemp()
+    ck = os.path.join(work, "checkpoints", "c")
+    os.makedirs(ck)
+    CLIPVisionModel(CLIPVisionConfig(hidden_size=64, intermediate_size=64, num_hidden_layers=1, num_attention_heads=1,
+                                     image_size=28, patch_size=14)).save_pretrained(ck)
+    CLIPImageProcessor().save_pretrained(ck)
+    cwd = os.getcwd()
+    os.chdir(work)
+    cfg = M.EventChatConfig(hidden_size=4096, num_hidden_layers=1, intermediate_size=64, num_attention_heads=32,
+                            vocab_size=1024, mm_visual_tower="c", event_feature_adaptor=True)
+    model = M.EventChatModel(cfg).float().eval()
+    os.chdir(cwd)
+    table, feats = splice_inputs()
+    with torch.no_grad():
+        model.get_model().embed_tokens.weight.copy_(table)
+        model.get_model().feature_adaptor.weight.copy_(torch.eye(4096))
+        model.get_model().feature_adaptor.bias.zero_()
+    g = torch.Generator().manual_seed(321)
+    L = 1700
+    ids = torch.randint(1, 1000, (3, L), generator=g)
+    mask = torch.ones(3, L, dtype=torch.long)
+    ids[0, 5] = -200; mask[0, 40:] = 0                       # one event token, short sample
+    ids[1, 3] = -200; ids[1, 1600] = -200                    # two event tokens, 1698 + 2*582 > 2048: truncated
+    mask[2, 100:] = 0; mask[2, 7] = 0                        # no event token, hole in the mask
+    labels = torch.where(torch.rand(3, L, generator=g) < 0.5, ids, torch.full_like(ids, -100))
+    with torch.no_grad():
+        out = model.prepare_inputs_labels_for_multimodal(ids, None, mask, None, labels, event_features=feats.clone())
+    _, pos, am, _, emb, lab = out
+    o_pos, o_am, o_emb, o_lab = osp.splice(table, ids, None, mask, labels, feats)
+    assert o_pos is None and pos is None and torch.equal(o_emb, emb) and torch.equal(o_am, am) and torch.equal(o_lab, lab)
+    pid = torch.arange(L)[None].expand(3, L).contiguous()
+    with torch.no_grad():
+        out2 = model.prepare_inputs_labels_for_multimodal(ids, pid, None, None, None, event_features=feats.clone())
+    o2 = osp.splice(table, ids, pid, None, None, feats)
+    assert out2[2] is None and o2[1] is None and out2[5] is None and o2[3] is None
+    assert torch.equal(out2[1], o2[0]) and torch.equal(out2[4], o2[2])
+    np.savez_compressed(os.path.join(OUT, "splice.npz"), ids=ids.numpy(), mask=mask.numpy(), labels=labels.numpy(),
+                        emb_sub=emb[:, :, ::64].numpy(), emb_rowsum=emb.double().sum(-1).numpy(), am=am.numpy(),
+                        lab=lab.numpy(), pos2=out2[1].numpy(), emb2_rowsum=out2[4].double().sum(-1).numpy())
+    print("splice golden written", tuple(emb.shape))
+
+
+def splice_inputs():
+    """Seeded embedding table [1024,4096] and event features [4,582,4096], bf16 representable."""
+    g = torch.Generator().manual_seed(123)
+    table = (torch.randn(1024, 4096, generator=g) * 0.02).bfloat16().float()
+    feats = torch.randn(4, 582, 4096, generator=g).bfloat16().float()
+    return table, feats
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "splice":
+        make_splice_golden()
+    else:
+        main()
+        make_splice_golden()

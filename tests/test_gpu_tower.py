@@ -206,3 +206,28 @@ def test_full_batch_properties(frontends, dev):
         one = fe.visual_tokens(x[b * N:(b + 1) * N], y[b * N:(b + 1) * N], p[b * N:(b + 1) * N],
                                torch.tensor([0, N], dtype=torch.int64, device=dev), (H, W))
         assert torch.equal(one[0], tok[b])
+
+
+def test_multimodal_splice_bit_exact(dev):
+    """prepare_inputs_labels_for_multimodal's splice (model/EventChatModel.py:355-465) through
+    egpt_splice_embeddings vs the reference's own output (tests/golden/splice.npz) and the oracle."""
+    from eventgpt_b200.model import splice_event_features
+    from oracle import splice as osp
+    from oracle.make_golden import splice_inputs
+    z = np.load(os.path.join(GOLDEN, "splice.npz"))
+    table, feats = splice_inputs()
+    ids, mask, labels = (torch.from_numpy(z[k]) for k in ("ids", "mask", "labels"))
+    td, fd = table.to(dev).bfloat16(), feats.to(dev).bfloat16()
+    pos, am, emb, lab = splice_event_features(td, ids, None, mask, labels, fd)
+    assert pos is None and emb.dtype == torch.bfloat16 and tuple(emb.shape) == (3, 2048, 4096)
+    e = emb.float().cpu()
+    assert np.array_equal(e[:, :, ::64].numpy(), z["emb_sub"]) and np.allclose(e.double().sum(-1).numpy(), z["emb_rowsum"])
+    assert np.array_equal(am.numpy(), z["am"]) and am.dtype == mask.dtype and np.array_equal(lab.numpy(), z["lab"])
+    o = osp.splice(table, ids, None, mask, labels, feats)
+    assert torch.equal(e, o[2])
+    pid = torch.arange(ids.shape[1])[None].expand(3, -1).contiguous()
+    pos2, am2, emb2, lab2 = splice_event_features(td, ids.to(dev), pid.to(dev), None, None, fd)
+    assert am2 is None and lab2 is None and pos2.is_cuda and np.array_equal(pos2.cpu().numpy(), z["pos2"])
+    assert np.allclose(emb2.float().cpu().double().sum(-1).numpy(), z["emb2_rowsum"])
+    with pytest.raises(IndexError):            # more <event> tokens than feature entries, as upstream
+        splice_event_features(td, ids, None, mask, labels, fd[:2])

@@ -101,3 +101,20 @@ def test_pooling_shapes_and_errors():
     assert ovit.get_spatio_temporal_features(f, 2).shape == (9, 3)
     with pytest.raises(ValueError):
         ovit.get_spatio_temporal_features(torch.randn(5, 7))
+
+
+def test_splice_matches_reference():
+    """model/EventChatModel.py:355-465 restated in oracle/splice.py vs the real reference's output."""
+    from oracle import splice as osp
+    from oracle.make_golden import splice_inputs
+    z = np.load(os.path.join(GOLDEN, "splice.npz"))
+    table, feats = splice_inputs()
+    ids, mask, labels = (torch.from_numpy(z[k]) for k in ("ids", "mask", "labels"))
+    pos, am, emb, lab = osp.splice(table, ids, None, mask, labels, feats)
+    assert pos is None and tuple(emb.shape) == (3, 2048, 4096)
+    assert np.array_equal(emb[:, :, ::64].numpy(), z["emb_sub"]) and np.allclose(emb.double().sum(-1).numpy(), z["emb_rowsum"])
+    assert np.array_equal(am.numpy(), z["am"]) and np.array_equal(lab.numpy(), z["lab"])
+    pid = torch.arange(ids.shape[1])[None].expand(3, -1).contiguous()
+    pos2, am2, emb2, lab2 = osp.splice(table, ids, pid, None, None, feats)
+    assert am2 is None and lab2 is None and np.array_equal(pos2.numpy(), z["pos2"])
+    assert np.allclose(emb2.double().sum(-1).numpy(), z["emb2_rowsum"])
