@@ -55,7 +55,8 @@ __device__ __forceinline__ float activate(float v) {
 template <int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                 const __grid_constant__ CUtensorMap tmap_out, const float* __restrict__ bias, long long M, int N, int K) {
+                 const __grid_constant__ CUtensorMap tmap_out, const float* __restrict__ bias, long long M, int N, int K,
+                 long long* __restrict__ stats) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* staging = smem + kStages * kStageBytes;                 // 1024-byte aligned
@@ -93,10 +94,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if (warp == 0 && lane == 0) {
     // ===== TMA producer =====
     int stage = 0; uint32_t phase = 0;
+    long long stat_prod_wait = 0;
     for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m0 = (int)(tile / n_tiles) * BM, n0 = (int)(tile % n_tiles) * BN;
       for (int kb = 0; kb < num_kb; ++kb) {
+#ifdef EGPT_GEMM_STATS
+        const long long w0 = clock64();
         ptx::mbar_wait(empty_bar + stage, phase ^ 1);
+        if (stats) stat_prod_wait += clock64() - w0;
+#else
+        ptx::mbar_wait(empty_bar + stage, phase ^ 1);
+#endif
         uint8_t* sa = smem + stage * kStageBytes;
         ptx::mbar_arrive_expect_tx(full_bar + stage, kStageBytes);
         ptx::tma_load_2d(sa, &tmap_a, full_bar + stage, kb * BK, m0);
@@ -104,17 +112,29 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
     }
+#ifdef EGPT_GEMM_STATS
+    if (stats) stats[blockIdx.x * 8 + 0] = stat_prod_wait;
+#endif
   } else if (warp == 1 && lane == 0) {
     // ===== MMA issuer =====
     constexpr uint32_t idesc = ptx::make_idesc_bf16(BM, BN);
     int stage = 0; uint32_t phase = 0;
     int acc = 0; uint32_t acc_phase = 0;
+    long long stat_full = 0, stat_tmem = 0; const long long stat_t0 = clock64();
     for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+#ifdef EGPT_GEMM_STATS
+      { const long long w0 = clock64(); ptx::mbar_wait(tmem_empty + acc, acc_phase ^ 1); stat_tmem += clock64() - w0; }
+#else
       ptx::mbar_wait(tmem_empty + acc, acc_phase ^ 1);
+#endif
       ptx::tcgen05_fence_after();
       const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
       for (int kb = 0; kb < num_kb; ++kb) {
+#ifdef EGPT_GEMM_STATS
+        { const long long w0 = clock64(); ptx::mbar_wait(full_bar + stage, phase); stat_full += clock64() - w0; }
+#else
         ptx::mbar_wait(full_bar + stage, phase);
+#endif
         ptx::tcgen05_fence_after();
         const uint32_t sa = ptx::smem_u32(smem + stage * kStageBytes);
         const uint64_t da = ptx::make_smem_desc_sw128(sa), db = ptx::make_smem_desc_sw128(sa + kABytes);
@@ -129,6 +149,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       ptx::umma_commit(tmem_full + acc);              // accumulator ready for the epilogue
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+#ifdef EGPT_GEMM_STATS
+    if (stats) { stats[blockIdx.x * 8 + 1] = stat_full; stats[blockIdx.x * 8 + 2] = stat_tmem; stats[blockIdx.x * 8 + 3] = clock64() - stat_t0; }
+#else
+    (void)stat_full; (void)stat_tmem; (void)stat_t0;
+#endif
   } else if (warp >= 4) {
     // ===== epilogue =====
     const int q = warp & 3;                            // TMEM lane quadrant this warp may read
@@ -240,7 +265,7 @@ static int make_tmap(CUtensorMap* map, const void* ptr, bool f32, uint64_t rows,
 
 template <int EPI>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const float* bias,
-                       long long M, int N, int K, cudaStream_t stream) {
+                       long long M, int N, int K, cudaStream_t stream, long long* stats = nullptr) {
   static std::once_flag once;   // attribute is per function; one process drives one device
   cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [&] {
@@ -249,13 +274,19 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
   EGPT_CUDA(attr_err);
   const long long tiles = ((M + BM - 1) / BM) * (N / BN);
   const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
-  gemm_bf16_kernel<EPI><<<grid, kGemmThreads, kGemmSmem, stream>>>(ta, tb, to, bias, M, N, K);
+  gemm_bf16_kernel<EPI><<<grid, kGemmThreads, kGemmSmem, stream>>>(ta, tb, to, bias, M, N, K, stats);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
 }
 
+int gemm_bf16_stats(const void* A, const void* B, const float* bias, void* out, long long M, int N, int K, int epilogue,
+                    cudaStream_t stream, long long* stats);
 int gemm_bf16(const void* A, const void* B, const float* bias, void* out, long long M, int N, int K, int epilogue,
               cudaStream_t stream) {
+  return gemm_bf16_stats(A, B, bias, out, M, N, K, epilogue, stream, nullptr);
+}
+int gemm_bf16_stats(const void* A, const void* B, const float* bias, void* out, long long M, int N, int K, int epilogue,
+                    cudaStream_t stream, long long* stats) {
   EGPT_CHECK_ARG(A && B && out, "gemm: null pointer");
   EGPT_CHECK_ARG(M > 0 && N > 0 && K > 0 && N % BN == 0 && K % BK == 0, "gemm: unsupported shape M=%lld N=%d K=%d (N %% 256, K %% 64)",
                  M, N, K);
@@ -269,11 +300,11 @@ int gemm_bf16(const void* A, const void* B, const float* bias, void* out, long l
   EGPT_TRY(make_tmap(&tb, B, false, (uint64_t)N, (uint64_t)K, BK, BN));
   EGPT_TRY(make_tmap(&to, out, f32_out, (uint64_t)M, (uint64_t)N, f32_out ? 32 : 64, 32));
   switch (epilogue) {
-    case EPI_BIAS_BF16: return launch_gemm<EPI_BIAS_BF16>(ta, tb, to, bias, M, N, K, stream);
-    case EPI_QUICKGELU_BF16: return launch_gemm<EPI_QUICKGELU_BF16>(ta, tb, to, bias, M, N, K, stream);
-    case EPI_GELU_BF16: return launch_gemm<EPI_GELU_BF16>(ta, tb, to, bias, M, N, K, stream);
-    case EPI_RESIDUAL_F32: return launch_gemm<EPI_RESIDUAL_F32>(ta, tb, to, bias, M, N, K, stream);
-    case EPI_STORE_F32: return launch_gemm<EPI_STORE_F32>(ta, tb, to, bias, M, N, K, stream);
+    case EPI_BIAS_BF16: return launch_gemm<EPI_BIAS_BF16>(ta, tb, to, bias, M, N, K, stream, stats);
+    case EPI_QUICKGELU_BF16: return launch_gemm<EPI_QUICKGELU_BF16>(ta, tb, to, bias, M, N, K, stream, stats);
+    case EPI_GELU_BF16: return launch_gemm<EPI_GELU_BF16>(ta, tb, to, bias, M, N, K, stream, stats);
+    case EPI_RESIDUAL_F32: return launch_gemm<EPI_RESIDUAL_F32>(ta, tb, to, bias, M, N, K, stream, stats);
+    case EPI_STORE_F32: return launch_gemm<EPI_STORE_F32>(ta, tb, to, bias, M, N, K, stream, stats);
   }
   set_error("gemm: unknown epilogue %d", epilogue);
   return EGPT_ERR_INVALID;
@@ -285,3 +316,11 @@ extern "C" int egpt_gemm_bf16(const uint16_t* A, const uint16_t* B, const float*
                               int K, int epilogue, void* stream) {
   return egpt::gemm_bf16(A, B, bias, out, M, N, K, epilogue, (cudaStream_t)stream);
 }
+
+#ifdef EGPT_GEMM_STATS
+// developer aid: per-CTA cycles {producer waiting for a free stage, MMA waiting for data, MMA waiting for TMEM, MMA total}
+extern "C" int egpt_gemm_stats(const uint16_t* A, const uint16_t* B, const float* bias, void* out, int64_t M, int N, int K,
+                               int epilogue, long long* stats, void* stream) {
+  return egpt::gemm_bf16_stats(A, B, bias, out, M, N, K, epilogue, (cudaStream_t)stream, stats);
+}
+#endif

@@ -76,6 +76,10 @@ def stage_events():
     print("EVENTS_BAD", bad)
 
 
+GEMM_TIMING = [(92320, 3072, 1024, 0), (92320, 1024, 1024, 3), (92320, 1024, 1024, 4), (92320, 1024, 1024, 0), (92320, 4096, 1024, 1),
+               (92320, 1024, 4096, 3), (92320, 1024, 4096, 4), (92320, 1024, 4096, 0), (92320, 4096, 4096, 0)]
+
+
 def stage_gemm():
     import torch
     from eventgpt_b200 import events as E
@@ -113,7 +117,7 @@ def stage_gemm():
             except Exception as ex:  # noqa
                 print(f"gemm M={M} N={N} K={K} epi={epi}: EXCEPTION {ex}")
                 return
-    for (M, N, K, epi) in [(92320, 3072, 1024, 0), (92320, 1024, 1024, 3), (92320, 4096, 1024, 1), (92320, 1024, 4096, 3), (92320, 4096, 4096, 0)]:
+    for (M, N, K, epi) in GEMM_TIMING:
         A = torch.randn(M, K, device=dev).bfloat16()
         B = torch.randn(N, K, device=dev).bfloat16()
         bias = torch.randn(N, device=dev)
