@@ -6,17 +6,22 @@
 // :84-85,338).  nn.Linear stores weight as [out, in] = [N, K] K-major, which is
 // exactly the B operand layout tcgen05 wants, so weights are used as they are.
 //
-// Structure (one CTA per SM, 256 threads):
-//   warp 0    TMA producer: A (128 x 64) and B (256 x 64) bf16 tiles, SWIZZLE_128B,
-//             4-stage mbarrier ring
-//   warp 1    MMA issuer: one thread issues tcgen05.mma (M128 N256 K16), fp32
-//             accumulators in TMEM, double-buffered (2 x 256 columns)
+// Structure: persistent, one CTA per SM, CTAs paired in clusters of 2 (tcgen05 cta_group::2), 256 threads:
+//   warp 0    TMA producer (both CTAs): own 128 x 64 slice of A and HALF (128 rows) of the 256 x 64 B tile,
+//             SWIZZLE_128B, 6-stage mbarrier ring (32 KB per stage per SM); completion bytes of both CTAs
+//             are credited to the leader CTA's "full" barrier
+//   warp 1    MMA issuer (leader CTA only): one thread issues tcgen05.mma.cta_group::2 (M256 N256 K16),
+//             fp32 accumulators in both CTAs' TMEM, double-buffered (2 x 256 columns); commits are
+//             multicast to both CTAs ("slot free", "accumulator ready")
 //   warp 2    TMEM allocator
-//   warps 4-7 epilogue: tcgen05.ld 32 lanes x 32 columns -> bias / activation -> 128-byte
-//             swizzled staging rows in shared memory -> TMA store (bf16 / fp32), or TMA
-//             reduce-add for the fp32 residual stream (h += acc + bias is done in L2;
-//             the SM never reads h).  Rows past M are clipped by the TMA unit.
-// Tiles are walked n-fastest so the CTAs running concurrently share A rows through L2.
+//   warps 4-7 epilogue (both CTAs, own 128 rows): tcgen05.ld 32 lanes x 32 columns -> bias / activation ->
+//             128-byte swizzled staging rows in shared memory -> TMA store (bf16 / fp32), or TMA reduce-add
+//             for the fp32 residual stream (h += acc + bias is done in L2; the SM never reads h).  Rows past
+//             M are clipped by the TMA unit.
+// Tiles are walked n-fastest so the CTA pairs running concurrently share A rows through L2.
+// Measured (profiles/r01_bench_history.md): a single-CTA 128x256 version with 4 x 48 KB stages spent 17-33 % of
+// the MMA thread's time waiting for operand data; pairing CTAs cut the L2 -> SM operand traffic by a third and
+// made room for six stages.
 #include "common.cuh"
 #include "sm100_ptx.cuh"
 #include <mutex>
@@ -24,14 +29,10 @@
 namespace egpt {
 
 constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16;
-constexpr int kStages = 4;
 constexpr int kABytes = BM * BK * 2;               // 16 KB
-constexpr int kBBytes = BN * BK * 2;               // 32 KB
-constexpr int kStageBytes = kABytes + kBBytes;     // 48 KB
 constexpr int kTmemCols = 2 * BN;                  // two accumulator stages
 constexpr int kGemmThreads = 256;
 constexpr int kStagingBytes = 4 * 2 * 4096;        // 4 epilogue warps x 2 buffers x (32 rows x 128 B)
-constexpr int kGemmSmem = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 
 enum { EPI_BIAS_BF16 = 0, EPI_QUICKGELU_BF16 = 1, EPI_GELU_BF16 = 2, EPI_RESIDUAL_F32 = 3, EPI_STORE_F32 = 4 };
 
@@ -52,25 +53,38 @@ __device__ __forceinline__ float activate(float v) {
   return v;
 }
 
+// ---- 2-CTA variant ------------------------------------------------------------------------------
+// A CTA pair (cluster of 2) computes a 256 x 256 tile with tcgen05.mma.cta_group::2: each CTA loads its own
+// 128 x 64 slice of A and HALF (128 rows) of the 256 x 64 B tile, so a stage costs 32 KB per SM instead of
+// 48 KB -> six stages fit where four did, and the L2 -> SM operand traffic drops by a third.  The leader
+// CTA issues the MMAs; full barriers live in the leader (both CTAs' TMA bytes are credited to them), empty /
+// accumulator-ready barriers are multicast to both CTAs; each CTA drains its own 128 accumulator rows.
+constexpr int kStages2 = 6;
+constexpr int kBHalfBytes = (BN / 2) * BK * 2;          // 16 KB
+constexpr int kStageBytes2 = kABytes + kBHalfBytes;     // 32 KB per CTA
+constexpr int kGemmSmem2 = kStages2 * kStageBytes2 + kStagingBytes + 1024 + 256;
+
 template <int EPI>
-__global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                 const __grid_constant__ CUtensorMap tmap_out, const float* __restrict__ bias, long long M, int N, int K,
-                 long long* __restrict__ stats) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                  const __grid_constant__ CUtensorMap tmap_out, const float* __restrict__ bias, long long M, int N, int K) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* staging = smem + kStages * kStageBytes;                 // 1024-byte aligned
+  uint8_t* staging = smem + kStages2 * kStageBytes2;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + kStagingBytes);
-  uint64_t* empty_bar = full_bar + kStages;
-  uint64_t* tmem_full = empty_bar + kStages;
+  uint64_t* empty_bar = full_bar + kStages2;
+  uint64_t* tmem_full = empty_bar + kStages2;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const bool leader = rank == 0;
   const int n_tiles = N / BN;
-  const long long m_tiles = (M + BM - 1) / BM;
-  const long long num_tiles = m_tiles * n_tiles;
+  const long long m_pairs = (M + 2 * BM - 1) / (2 * BM);
+  const long long num_tiles = m_pairs * n_tiles;           // pair tiles
   const int num_kb = K / BK;
+  const long long first = blockIdx.x >> 1, step = gridDim.x >> 1;
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tmap_a);
@@ -78,92 +92,68 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     ptx::prefetch_tensormap(&tmap_out);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < kStages; ++i) { ptx::mbar_init(full_bar + i, 1); ptx::mbar_init(empty_bar + i, 1); }
-    for (int i = 0; i < 2; ++i) { ptx::mbar_init(tmem_full + i, 1); ptx::mbar_init(tmem_empty + i, 128); }
+    for (int i = 0; i < kStages2; ++i) { ptx::mbar_init(full_bar + i, 1); ptx::mbar_init(empty_bar + i, 1); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(tmem_full + i, 1); ptx::mbar_init(tmem_empty + i, 256); }
     ptx::fence_barrier_init();
   }
   if (warp == 2) {
-    ptx::tmem_alloc(tmem_ptr, kTmemCols);
-    ptx::tmem_relinquish();
+    ptx::tmem_alloc_2sm(tmem_ptr, kTmemCols);
+    ptx::tmem_relinquish_2sm();
   }
   ptx::tcgen05_fence_before();
-  __syncthreads();
+  ptx::cluster_sync_all();                                  // barriers of both CTAs initialised before anyone signals them
   ptx::tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
   if (warp == 0 && lane == 0) {
-    // ===== TMA producer =====
+    // ===== TMA producer (both CTAs) =====
     int stage = 0; uint32_t phase = 0;
-    long long stat_prod_wait = 0;
-    for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m0 = (int)(tile / n_tiles) * BM, n0 = (int)(tile % n_tiles) * BN;
+    for (long long tile = first; tile < num_tiles; tile += step) {
+      const int m0 = (int)(tile / n_tiles) * (2 * BM) + (int)rank * BM;
+      const int n0 = (int)(tile % n_tiles) * BN + (int)rank * (BN / 2);
       for (int kb = 0; kb < num_kb; ++kb) {
-#ifdef EGPT_GEMM_STATS
-        const long long w0 = clock64();
         ptx::mbar_wait(empty_bar + stage, phase ^ 1);
-        if (stats) stat_prod_wait += clock64() - w0;
-#else
-        ptx::mbar_wait(empty_bar + stage, phase ^ 1);
-#endif
-        uint8_t* sa = smem + stage * kStageBytes;
-        ptx::mbar_arrive_expect_tx(full_bar + stage, kStageBytes);
-        ptx::tma_load_2d(sa, &tmap_a, full_bar + stage, kb * BK, m0);
-        ptx::tma_load_2d(sa + kABytes, &tmap_b, full_bar + stage, kb * BK, n0);
-        if (++stage == kStages) { stage = 0; phase ^= 1; }
+        uint8_t* sa = smem + stage * kStageBytes2;
+        if (leader) ptx::mbar_arrive_expect_tx(full_bar + stage, 2 * kStageBytes2);   // bytes of both CTAs
+        ptx::tma_load_2d_2sm(sa, &tmap_a, full_bar + stage, kb * BK, m0);
+        ptx::tma_load_2d_2sm(sa + kABytes, &tmap_b, full_bar + stage, kb * BK, n0);
+        if (++stage == kStages2) { stage = 0; phase ^= 1; }
       }
     }
-#ifdef EGPT_GEMM_STATS
-    if (stats) stats[blockIdx.x * 8 + 0] = stat_prod_wait;
-#endif
-  } else if (warp == 1 && lane == 0) {
-    // ===== MMA issuer =====
-    constexpr uint32_t idesc = ptx::make_idesc_bf16(BM, BN);
+  } else if (warp == 1 && lane == 0 && leader) {
+    // ===== MMA issuer (leader CTA only) =====
+    constexpr uint32_t idesc = ptx::make_idesc_bf16(2 * BM, BN);
     int stage = 0; uint32_t phase = 0;
     int acc = 0; uint32_t acc_phase = 0;
-    long long stat_full = 0, stat_tmem = 0; const long long stat_t0 = clock64();
-    for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-#ifdef EGPT_GEMM_STATS
-      { const long long w0 = clock64(); ptx::mbar_wait(tmem_empty + acc, acc_phase ^ 1); stat_tmem += clock64() - w0; }
-#else
-      ptx::mbar_wait(tmem_empty + acc, acc_phase ^ 1);
-#endif
+    for (long long tile = first; tile < num_tiles; tile += step) {
+      ptx::mbar_wait(tmem_empty + acc, acc_phase ^ 1);        // both CTAs' epilogues have drained this stage
       ptx::tcgen05_fence_after();
       const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
       for (int kb = 0; kb < num_kb; ++kb) {
-#ifdef EGPT_GEMM_STATS
-        { const long long w0 = clock64(); ptx::mbar_wait(full_bar + stage, phase); stat_full += clock64() - w0; }
-#else
         ptx::mbar_wait(full_bar + stage, phase);
-#endif
         ptx::tcgen05_fence_after();
-        const uint32_t sa = ptx::smem_u32(smem + stage * kStageBytes);
+        const uint32_t sa = ptx::smem_u32(smem + stage * kStageBytes2);
         const uint64_t da = ptx::make_smem_desc_sw128(sa), db = ptx::make_smem_desc_sw128(sa + kABytes);
 #pragma unroll
-        for (int k = 0; k < BK / UMMA_K; ++k) {
-          // advance 32 B (16 bf16) inside the 128 B swizzle atom: +2 in 16-byte units
-          ptx::umma_bf16_ss(tmem_d, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
-        }
-        ptx::umma_commit(empty_bar + stage);          // smem slot free once these MMAs retire
-        if (++stage == kStages) { stage = 0; phase ^= 1; }
+        for (int k = 0; k < BK / UMMA_K; ++k)
+          ptx::umma_bf16_ss_2sm(tmem_d, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+        ptx::umma_commit_2sm(empty_bar + stage);              // both producers may refill this slot
+        if (++stage == kStages2) { stage = 0; phase ^= 1; }
       }
-      ptx::umma_commit(tmem_full + acc);              // accumulator ready for the epilogue
+      ptx::umma_commit_2sm(tmem_full + acc);                  // both epilogues may read their accumulator half
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-#ifdef EGPT_GEMM_STATS
-    if (stats) { stats[blockIdx.x * 8 + 1] = stat_full; stats[blockIdx.x * 8 + 2] = stat_tmem; stats[blockIdx.x * 8 + 3] = clock64() - stat_t0; }
-#else
-    (void)stat_full; (void)stat_tmem; (void)stat_t0;
-#endif
   } else if (warp >= 4) {
-    // ===== epilogue =====
-    const int q = warp & 3;                            // TMEM lane quadrant this warp may read
+    // ===== epilogue (both CTAs, own 128 rows) =====
+    const int q = warp & 3;
     constexpr bool kF32Out = (EPI == EPI_RESIDUAL_F32 || EPI == EPI_STORE_F32);
-    constexpr int CH = kF32Out ? 32 : 64;              // columns per staged chunk (128 B per row)
+    constexpr int CH = kF32Out ? 32 : 64;
     uint8_t* my_stage = staging + q * 8192;
-    const uint32_t sw = (uint32_t)(lane & 7);          // SWIZZLE_128B: 16-byte chunk index ^= row & 7
+    const uint32_t sw = (uint32_t)(lane & 7);
+    const uint32_t leader_tmem_empty = ptx::mapa_u32(tmem_empty, 0);
     int acc = 0; uint32_t acc_phase = 0; int buf = 0;
-    for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int row0 = (int)(tile / n_tiles) * BM + q * 32;
+    for (long long tile = first; tile < num_tiles; tile += step) {
+      const int row0 = (int)(tile / n_tiles) * (2 * BM) + (int)rank * BM + q * 32;
       const int n0 = (int)(tile % n_tiles) * BN;
       ptx::mbar_wait(tmem_full + acc, acc_phase);
       ptx::tcgen05_fence_after();
@@ -174,11 +164,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
         if (CH == 64) ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0 + 32u, *reinterpret_cast<uint32_t(*)[32]>(&r[CH - 32]));
         ptx::tmem_ld_wait();
-        if (c0 + CH == BN) {                           // accumulator fully read: hand it back to the MMA warp
+        if (c0 + CH == BN) {
           ptx::tcgen05_fence_before();
-          ptx::mbar_arrive(tmem_empty + acc);
+          ptx::mbar_arrive_cluster(leader_tmem_empty + (uint32_t)(acc * 8));
         }
-        // the TMA store that last used this staging buffer must have finished reading it
         if (lane == 0) ptx::bulk_wait_group_read<1>();
         __syncwarp();
         uint8_t* dst = my_stage + buf * 4096 + lane * 128;
@@ -208,7 +197,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             *reinterpret_cast<uint4*>(dst + (((uint32_t)j ^ sw) << 4)) = o;
           }
         }
-        ptx::fence_proxy_async();                      // generic-proxy smem writes -> visible to the TMA unit
+        ptx::fence_proxy_async();
         __syncwarp();
         if (lane == 0) {
           if (EPI == EPI_RESIDUAL_F32) ptx::tma_reduce_add_2d(&tmap_out, my_stage + buf * 4096, n0 + c0, row0);
@@ -219,13 +208,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-    if (lane == 0) ptx::bulk_wait_group<0>();          // all stores / reductions complete before exit
+    if (lane == 0) ptx::bulk_wait_group<0>();
   }
 
   ptx::tcgen05_fence_before();
-  __syncthreads();
+  ptx::cluster_sync_all();                                   // nobody frees TMEM or exits while the peer still uses it
   ptx::tcgen05_fence_after();
-  if (warp == 2) ptx::tmem_dealloc(tmem_base, kTmemCols);
+  if (warp == 2) ptx::tmem_dealloc_2sm(tmem_base, kTmemCols);
 }
 
 // ---- host side -----------------------------------------------------------------------------------
@@ -264,47 +253,40 @@ static int make_tmap(CUtensorMap* map, const void* ptr, bool f32, uint64_t rows,
 }
 
 template <int EPI>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const float* bias,
-                       long long M, int N, int K, cudaStream_t stream, long long* stats = nullptr) {
-  static std::once_flag once;   // attribute is per function; one process drives one device
+static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const float* bias,
+                        long long M, int N, int K, cudaStream_t stream) {
+  static std::once_flag once;
   cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(gemm_bf16_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem);
+    attr_err = cudaFuncSetAttribute(gemm2_bf16_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem2);
   });
   EGPT_CUDA(attr_err);
-  const long long tiles = ((M + BM - 1) / BM) * (N / BN);
-  const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
-  gemm_bf16_kernel<EPI><<<grid, kGemmThreads, kGemmSmem, stream>>>(ta, tb, to, bias, M, N, K, stats);
+  const long long pairs = ((M + 2 * BM - 1) / (2 * BM)) * (N / BN);
+  const int grid = (int)(2 * (pairs < kNumSMs / 2 ? pairs : kNumSMs / 2));
+  gemm2_bf16_kernel<EPI><<<grid, kGemmThreads, kGemmSmem2, stream>>>(ta, tb, to, bias, M, N, K);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
 }
 
-int gemm_bf16_stats(const void* A, const void* B, const float* bias, void* out, long long M, int N, int K, int epilogue,
-                    cudaStream_t stream, long long* stats);
 int gemm_bf16(const void* A, const void* B, const float* bias, void* out, long long M, int N, int K, int epilogue,
               cudaStream_t stream) {
-  return gemm_bf16_stats(A, B, bias, out, M, N, K, epilogue, stream, nullptr);
-}
-int gemm_bf16_stats(const void* A, const void* B, const float* bias, void* out, long long M, int N, int K, int epilogue,
-                    cudaStream_t stream, long long* stats) {
   EGPT_CHECK_ARG(A && B && out, "gemm: null pointer");
   EGPT_CHECK_ARG(M > 0 && N > 0 && K > 0 && N % BN == 0 && K % BK == 0, "gemm: unsupported shape M=%lld N=%d K=%d (N %% 256, K %% 64)",
                  M, N, K);
   EGPT_CHECK_ARG(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
                  (bias == nullptr || (uintptr_t)bias % 16 == 0), "gemm: pointers must be 16-byte aligned");
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, to;
   ProfScope prof(PROF_GEMM, 2.0 * (double)M * N * K, stream);
-  CUtensorMap to;
   const bool f32_out = epilogue == EPI_RESIDUAL_F32 || epilogue == EPI_STORE_F32;
   EGPT_TRY(make_tmap(&ta, A, false, (uint64_t)M, (uint64_t)K, BK, BM));
-  EGPT_TRY(make_tmap(&tb, B, false, (uint64_t)N, (uint64_t)K, BK, BN));
+  EGPT_TRY(make_tmap(&tb, B, false, (uint64_t)N, (uint64_t)K, BK, BN / 2));          // each CTA of a pair loads half of B
   EGPT_TRY(make_tmap(&to, out, f32_out, (uint64_t)M, (uint64_t)N, f32_out ? 32 : 64, 32));
   switch (epilogue) {
-    case EPI_BIAS_BF16: return launch_gemm<EPI_BIAS_BF16>(ta, tb, to, bias, M, N, K, stream, stats);
-    case EPI_QUICKGELU_BF16: return launch_gemm<EPI_QUICKGELU_BF16>(ta, tb, to, bias, M, N, K, stream, stats);
-    case EPI_GELU_BF16: return launch_gemm<EPI_GELU_BF16>(ta, tb, to, bias, M, N, K, stream, stats);
-    case EPI_RESIDUAL_F32: return launch_gemm<EPI_RESIDUAL_F32>(ta, tb, to, bias, M, N, K, stream, stats);
-    case EPI_STORE_F32: return launch_gemm<EPI_STORE_F32>(ta, tb, to, bias, M, N, K, stream, stats);
+    case EPI_BIAS_BF16: return launch_gemm2<EPI_BIAS_BF16>(ta, tb, to, bias, M, N, K, stream);
+    case EPI_QUICKGELU_BF16: return launch_gemm2<EPI_QUICKGELU_BF16>(ta, tb, to, bias, M, N, K, stream);
+    case EPI_GELU_BF16: return launch_gemm2<EPI_GELU_BF16>(ta, tb, to, bias, M, N, K, stream);
+    case EPI_RESIDUAL_F32: return launch_gemm2<EPI_RESIDUAL_F32>(ta, tb, to, bias, M, N, K, stream);
+    case EPI_STORE_F32: return launch_gemm2<EPI_STORE_F32>(ta, tb, to, bias, M, N, K, stream);
   }
   set_error("gemm: unknown epilogue %d", epilogue);
   return EGPT_ERR_INVALID;
@@ -316,11 +298,3 @@ extern "C" int egpt_gemm_bf16(const uint16_t* A, const uint16_t* B, const float*
                               int K, int epilogue, void* stream) {
   return egpt::gemm_bf16(A, B, bias, out, M, N, K, epilogue, (cudaStream_t)stream);
 }
-
-#ifdef EGPT_GEMM_STATS
-// developer aid: per-CTA cycles {producer waiting for a free stage, MMA waiting for data, MMA waiting for TMEM, MMA total}
-extern "C" int egpt_gemm_stats(const uint16_t* A, const uint16_t* B, const float* bias, void* out, int64_t M, int N, int K,
-                               int epilogue, long long* stats, void* stream) {
-  return egpt::gemm_bf16_stats(A, B, bias, out, M, N, K, epilogue, (cudaStream_t)stream, stats);
-}
-#endif
