@@ -102,28 +102,52 @@ __device__ __forceinline__ int clip8(int v) {
 }
 
 // Horizontal pass: tmp[f][y][o][c] for every input row y < h and the 336 cropped columns.
-// grid (ceil(H/8), F), 352 threads; thread o owns output column o for 8 rows.
+// grid (ceil(H/8), F), 352 threads.  The CTA first stages its 8 input rows in shared memory with 16-byte
+// loads (rows are packed at an arbitrary byte offset, so each is copied from the enclosing aligned span);
+// thread o then owns output column o and reads its taps as bytes from shared memory.
+constexpr int kHRows = 8;
 __global__ void __launch_bounds__(352)
 resample_horizontal_kernel(const uint8_t* __restrict__ frames, size_t frame_stride, const int32_t* __restrict__ hw,
-                           const int32_t* __restrict__ tables, uint8_t* __restrict__ tmp, size_t tmp_stride) {
+                           const int32_t* __restrict__ tables, uint8_t* __restrict__ tmp, size_t tmp_stride, int pitch) {
+  extern __shared__ __align__(16) uint8_t srows[];          // [kHRows][pitch], pitch % 16 == 0 (0: no staging)
   const int f = blockIdx.y, o = threadIdx.x;
   const int h = hw[2 * f], w = hw[2 * f + 1];
-  const int y0 = blockIdx.x * 8;
-  if (o >= kCrop || y0 >= h) return;
+  const int y0 = blockIdx.x * kHRows;
+  if (y0 >= h) return;
+  const int y1 = min(y0 + kHRows, h);
+  const uint8_t* src = frames + (size_t)f * frame_stride;
+  const bool staged = pitch > 0 && 3 * w + 32 <= pitch;
+  if (staged) {
+    for (int r = 0; r < y1 - y0; ++r) {
+      const size_t gs = (size_t)(y0 + r) * w * 3, a0 = gs & ~(size_t)15;
+      const int nvec = (int)((gs + (size_t)w * 3 - a0 + 15) >> 4);
+      const uint4* g = reinterpret_cast<const uint4*>(src + a0);
+      uint4* d = reinterpret_cast<uint4*>(srows + r * pitch);
+      for (int i = threadIdx.x; i < nvec; i += blockDim.x) d[i] = __ldg(g + i);
+    }
+    __syncthreads();
+  }
+  if (o >= kCrop) return;
   const int32_t* tab = tables + ((size_t)f * 2 + 0) * kAxisInts;
   const int xmin = tab[o], cnt = tab[kCrop + o];
   const int32_t* k = tab + 2 * kCrop + o * kTaps;
-  const uint8_t* src = frames + (size_t)f * frame_stride;
+  int kr[12];
+#pragma unroll
+  for (int j = 0; j < 12; ++j) kr[j] = j < cnt ? __ldg(k + j) : 0;
   uint8_t* dst = tmp + (size_t)f * tmp_stride;
-  const int y1 = min(y0 + 8, h);
   for (int y = y0; y < y1; ++y) {
-    const uint8_t* row = src + ((size_t)y * w + xmin) * 3;
+    const size_t gs = (size_t)y * w * 3;
+    const uint8_t* row = staged ? srows + (y - y0) * pitch + (gs & 15) + xmin * 3 : src + gs + (size_t)xmin * 3;
     int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
-    for (int j = 0; j < cnt; ++j) {
-      const int kj = __ldg(k + j);
-      a0 += row[3 * j + 0] * kj;
-      a1 += row[3 * j + 1] * kj;
-      a2 += row[3 * j + 2] * kj;
+    if (cnt <= 12) {
+#pragma unroll
+      for (int j = 0; j < 12; ++j)
+        if (j < cnt) { a0 += row[3 * j + 0] * kr[j]; a1 += row[3 * j + 1] * kr[j]; a2 += row[3 * j + 2] * kr[j]; }
+    } else {
+      for (int j = 0; j < cnt; ++j) {
+        const int kj = __ldg(k + j);
+        a0 += row[3 * j + 0] * kj; a1 += row[3 * j + 1] * kj; a2 += row[3 * j + 2] * kj;
+      }
     }
     uint8_t* d = dst + ((size_t)y * kCrop + o) * 3;
     d[0] = (uint8_t)clip8(a0); d[1] = (uint8_t)clip8(a1); d[2] = (uint8_t)clip8(a2);
@@ -132,29 +156,47 @@ resample_horizontal_kernel(const uint8_t* __restrict__ frames, size_t frame_stri
 
 struct NormLut { uint16_t v[256 * 3]; };   // bf16 bits of ((u/255) - mean_c) / std_c, [u][c]
 
-// Vertical pass + crop + normalise + layout.  grid (336/8, F), 352 threads; thread o owns
-// output column o for 8 output rows.
+// Vertical pass + crop + normalise + layout.  grid (336/8, F), 352 threads; thread o owns output column o for
+// 8 output rows.  The rows of the horizontal intermediate that those 8 outputs need are staged in shared
+// memory first (up to kVRows of them; a frame so tall that more are needed reads global memory instead).
+constexpr int kVRows = 40;
+constexpr int kTmpRowBytes = kCrop * 3;                    // 1008 = 63 x 16
 __global__ void __launch_bounds__(352)
 resample_vertical_kernel(const uint8_t* __restrict__ tmp, size_t tmp_stride, const int32_t* __restrict__ hw,
                          const int32_t* __restrict__ tables, const NormLut lut,
                          uint16_t* __restrict__ out_pix, uint16_t* __restrict__ out_patches) {
   __shared__ uint16_t slut[256 * 3];
+  __shared__ __align__(16) uint8_t srows[kVRows * kTmpRowBytes];
   for (int i = threadIdx.x; i < 256 * 3; i += blockDim.x) slut[i] = lut.v[i];
-  __syncthreads();
   const int f = blockIdx.y, o = threadIdx.x;
   const int h = hw[2 * f];
   const int32_t* tab = tables + ((size_t)f * 2 + 1) * kAxisInts;
   const uint8_t* src = tmp + (size_t)f * tmp_stride;
   const int yo0 = blockIdx.x * 8;
+  int rbase = 0, rend = 0;
+  bool staged = false;
+  if (h > 0) {
+    rbase = tab[yo0];
+    rend = tab[yo0 + 7] + tab[kCrop + yo0 + 7];
+    staged = rend - rbase <= kVRows;
+    if (staged) {
+      const uint4* g = reinterpret_cast<const uint4*>(src + (size_t)rbase * kTmpRowBytes);
+      uint4* d = reinterpret_cast<uint4*>(srows);
+      const int nvec = (rend - rbase) * (kTmpRowBytes / 16);
+      for (int i = threadIdx.x; i < nvec; i += blockDim.x) d[i] = __ldg(g + i);
+    }
+  }
+  __syncthreads();
   if (o < kCrop && h > 0) {
     for (int yo = yo0; yo < yo0 + 8; ++yo) {
       const int ymin = tab[yo], cnt = tab[kCrop + yo];
       const int32_t* k = tab + 2 * kCrop + yo * kTaps;
-      const uint8_t* col = src + ((size_t)ymin * kCrop + o) * 3;
+      const uint8_t* col = staged ? srows + (size_t)(ymin - rbase) * kTmpRowBytes + o * 3
+                                  : src + ((size_t)ymin * kCrop + o) * 3;
       int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
       for (int j = 0; j < cnt; ++j) {
         const int kj = __ldg(k + j);
-        const uint8_t* q = col + (size_t)j * kCrop * 3;
+        const uint8_t* q = col + (size_t)j * kTmpRowBytes;
         a0 += q[0] * kj; a1 += q[1] * kj; a2 += q[2] * kj;
       }
       const uint16_t v0 = slut[clip8(a0) * 3 + 0], v1 = slut[clip8(a1) * 3 + 1], v2 = slut[clip8(a2) * 3 + 2];
@@ -239,7 +281,11 @@ extern "C" int egpt_preprocess(const uint8_t* frames, size_t frame_stride, const
   const size_t tmp_stride = tmp_stride_bytes(max_h);
   resize_coeffs_kernel<<<dim3(F, 2), 352, 0, stream>>>(hw, tables, status);
   EGPT_LAUNCH_CHECK();
-  resample_horizontal_kernel<<<dim3((max_h + 7) / 8, F), 352, 0, stream>>>(frames, frame_stride, hw, tables, tmp, tmp_stride);
+  // staging pitch: frames written with capacity (max_h, W) have frame_stride >= 3 * max_h * W
+  int pitch = (int)align_up(frame_stride / (size_t)max_h + 3 + 32, 16);
+  if ((size_t)pitch * kHRows > 40 * 1024) pitch = 0;       // very wide frames: no staging
+  resample_horizontal_kernel<<<dim3((max_h + kHRows - 1) / kHRows, F), 352, (size_t)pitch * kHRows, stream>>>(
+      frames, frame_stride, hw, tables, tmp, tmp_stride, pitch);
   EGPT_LAUNCH_CHECK();
   resample_vertical_kernel<<<dim3(kCrop / 8, F), 352, 0, stream>>>(tmp, tmp_stride, hw, tables, lut, out_pixel_values, out_patches);
   EGPT_LAUNCH_CHECK();

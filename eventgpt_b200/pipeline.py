@@ -1,0 +1,76 @@
+"""Host-fed serving loop: event windows arrive in pinned host memory, tokens leave to pinned host
+memory, and the copies of neighbouring batches overlap the compute of the current one.
+
+The reference processes one sample at a time on one stream
+(``inference.py:49-63``: ``process_event_data`` -> ``model.generate``); its only multi-stream
+consumer runs two prefills on separate CUDA streams (``pipeline/benchmark_e2e/benchmark_e2e_wallclock.py:641-649``).
+Here the same work is pipelined over three streams with two buffer slots:
+
+    copy-in  stream : events H2D of batch i+1
+    compute  stream : egpt_visual_tokens of batch i        (the caller's current stream)
+    copy-out stream : tokens D2H of batch i-1
+"""
+import torch
+
+from . import events as E
+
+TOKENS, LLM = 577, 4096
+
+
+class VisualTokenStream:
+    """Double-buffered host -> tokens -> host loop around ``EventGPTVisualFrontEnd.visual_tokens``."""
+
+    def __init__(self, frontend, max_events, max_windows, sensor_size, n_frames=E.N_FRAMES, depth=2):
+        self.fe, self.dev = frontend, frontend.device
+        self.sensor, self.n_frames, self.depth = sensor_size, n_frames, depth
+        d = self.dev
+        self.dx = [torch.empty(max_events, dtype=torch.uint16, device=d) for _ in range(depth)]
+        self.dy = [torch.empty(max_events, dtype=torch.uint16, device=d) for _ in range(depth)]
+        self.dp = [torch.empty(max_events, dtype=torch.uint8, device=d) for _ in range(depth)]
+        self.doff = [torch.empty(max_windows + 1, dtype=torch.int64, device=d) for _ in range(depth)]
+        self.tok = [torch.empty((max_windows, n_frames + TOKENS, LLM), dtype=torch.bfloat16, device=d) for _ in range(depth)]
+        self.htok = [torch.empty((max_windows, n_frames + TOKENS, LLM), dtype=torch.bfloat16).pin_memory() for _ in range(depth)]
+        self.s_in, self.s_out = torch.cuda.Stream(d), torch.cuda.Stream(d)
+        self.ev_h2d = [torch.cuda.Event() for _ in range(depth)]
+        self.ev_done = [torch.cuda.Event() for _ in range(depth)]
+        self.ev_d2h = [torch.cuda.Event() for _ in range(depth)]
+        self.count = 0
+
+    def submit(self, hx, hy, hp, hoff, post=None):
+        """Enqueue one batch (pinned host tensors: x, y uint16; p uint8; window offsets int64 [B+1]).
+        Returns the slot whose pinned ``htok[slot][:B]`` holds the tokens once ``wait(slot)`` returns."""
+        i, s = self.count, self.count % self.depth
+        self.count += 1
+        n, B = hx.numel(), hoff.numel() - 1
+        compute = torch.cuda.current_stream(self.dev)
+        if i >= self.depth:
+            self.s_in.wait_event(self.ev_done[s])          # slot's device inputs were consumed by batch i-depth
+        else:
+            self.s_in.wait_stream(compute)
+        with torch.cuda.stream(self.s_in):
+            self.dx[s][:n].copy_(hx, non_blocking=True)
+            self.dy[s][:n].copy_(hy, non_blocking=True)
+            self.dp[s][:n].copy_(hp, non_blocking=True)
+            self.doff[s][:B + 1].copy_(hoff, non_blocking=True)
+            self.ev_h2d[s].record(self.s_in)
+        compute.wait_event(self.ev_h2d[s])
+        if i >= self.depth:
+            compute.wait_event(self.ev_d2h[s])             # slot's token buffer was read out
+        self.fe.visual_tokens(self.dx[s][:n], self.dy[s][:n], self.dp[s][:n], self.doff[s][:B + 1], self.sensor,
+                              n_frames=self.n_frames, out=self.tok[s][:B], check_flags=False)
+        if post is not None:
+            post(self.tok[s][:B])                          # e.g. the final all_gather of a multi-GPU job
+        self.ev_done[s].record(compute)
+        self.s_out.wait_event(self.ev_done[s])
+        with torch.cuda.stream(self.s_out):
+            self.htok[s][:B].copy_(self.tok[s][:B], non_blocking=True)
+            self.ev_d2h[s].record(self.s_out)
+        return s
+
+    def wait(self, slot):
+        self.ev_d2h[slot].synchronize()
+        return self.htok[slot]
+
+    def drain(self):
+        self.s_out.synchronize()
+        torch.cuda.current_stream(self.dev).synchronize()

@@ -231,3 +231,29 @@ def test_multimodal_splice_bit_exact(dev):
     assert np.allclose(emb2.float().cpu().double().sum(-1).numpy(), z["emb2_rowsum"])
     with pytest.raises(IndexError):            # more <event> tokens than feature entries, as upstream
         splice_event_features(td, ids, None, mask, labels, fd[:2])
+
+
+def test_host_fed_stream_matches_direct_call(frontends, dev):
+    """eventgpt_b200.pipeline.VisualTokenStream (pinned host events in, pinned host tokens out, copies overlapped
+    with compute over two slots) returns exactly what the direct device call returns, batch after batch."""
+    from eventgpt_b200 import events as E
+    from eventgpt_b200.pipeline import VisualTokenStream
+    sd, fe = frontends(2)
+    rng = np.random.default_rng(7)
+    B, N, H, W = 2, 60_000, 240, 320
+    vs = VisualTokenStream(fe, B * N, B, (H, W))
+    batches, slots = [], []
+    for i in range(5):                                   # more batches than slots: buffers are reused
+        hx = torch.from_numpy(rng.integers(0, W, B * N).astype(np.uint16)).pin_memory()
+        hy = torch.from_numpy(rng.integers(0, H, B * N).astype(np.uint16)).pin_memory()
+        hp = torch.from_numpy(rng.integers(0, 2, B * N).astype(np.uint8)).pin_memory()
+        hoff = (torch.arange(0, B + 1, dtype=torch.int64) * N).pin_memory()
+        batches.append((hx, hy, hp, hoff))
+    got = []
+    for b in batches:
+        s = vs.submit(*b)
+        got.append(vs.wait(s)[:B].clone())               # read the slot before it is reused
+    vs.drain()
+    for (hx, hy, hp, hoff), g in zip(batches, got):
+        want = fe.visual_tokens(hx.to(dev), hy.to(dev), hp.to(dev), hoff.to(dev), (H, W)).cpu()
+        assert torch.equal(g, want)
