@@ -273,7 +273,7 @@ def run_ours(args, rank, world, local_rank):
                     "api": "eventgpt_b200.pipeline.VisualTokenStream.submit (H2D / compute / D2H on three streams, two slots)"},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"kernel": "gemm_bf16_kernel (tcgen05, all tower/projector/adaptor linears)", "bound": "tensor",
+            "roofline": {"kernel": "gemm2_bf16_kernel (tcgen05 cta_group::2, all tower/projector/adaptor linears)", "bound": "tensor",
                          "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": traffic,
                          "peak_source": f"{pk_src} bf16_tflops_sustained (kernel timed inside a long step)",
