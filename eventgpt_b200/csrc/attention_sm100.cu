@@ -9,12 +9,14 @@
 //   warp 9     MMA issuer (one thread): S_j = Q K_j^T (M128 x N192 x K64) into a double-buffered TMEM
 //              region, then O_j = P_j V_j (M128 x N64 x K192; P read straight from TMEM where the
 //              softmax warps wrote it over S_j, V from shared memory as an MN-major operand)
-//   warp 10    TMEM allocator (512 columns: 2 x 192 for S, 2 x 64 for the per-block O)
+//   warp 10    TMEM allocator (512 columns: 2 x 192 for S, 2 x 64 for the output of even / odd tiles)
 //   warps 0-7  softmax: two threads per query row, each owning half of the key columns of a block
 //              and half of the 64 output dims.  S_j is read from TMEM once into registers, the
 //              row maximum is exchanged with the partner thread through shared memory, P_j goes
-//              back into the same TMEM columns as packed bf16 (tcgen05.st); the running output
-//              lives in registers (O = O * alpha + O_j), so TMEM never has to be rescaled.
+//              back into the same TMEM columns as packed bf16 (tcgen05.st).  The output accumulates
+//              in TMEM across the key blocks of a tile; it is rescaled in place only when a block
+//              raises a row's maximum by more than 2^8 (otherwise the stale maximum is kept: p <= 256
+//              is harmless in fp32 / bf16), so the common path is load S, max, exp2, store P.
 // Keys are walked in four blocks of 192, 192, 192 and 16 (= 592 >= 577).
 #include "common.cuh"
 #include "sm100_ptx.cuh"
@@ -130,7 +132,8 @@ struct Bars {
   uint64_t q_full, q_empty;
   uint64_t s_full[2];
   uint64_t p_full[2];
-  uint64_t o_full[2], o_empty[2];
+  uint64_t o_done[2];                    // [block parity]: the P V product of a block has retired
+  uint64_t o_free[2];                    // [tile parity]: the tile's output was read out of TMEM
   uint32_t tmem_ptr;
 };
 
@@ -154,7 +157,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
     ptx::mbar_init(&bars->q_full, 1); ptx::mbar_init(&bars->q_empty, 1);
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(&bars->s_full[i], 1); ptx::mbar_init(&bars->p_full[i], 256);
-      ptx::mbar_init(&bars->o_full[i], 1); ptx::mbar_init(&bars->o_empty[i], 256);
+      ptx::mbar_init(&bars->o_done[i], 1); ptx::mbar_init(&bars->o_free[i], 256);
     }
     ptx::fence_barrier_init();
   }
@@ -210,21 +213,23 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
       if (g < 12) TR(256 + g * 8 + 2);
       ptx::mbar_wait(&bars->p_full[b], (uint32_t)(n & 1));
       if (g < 12) TR(256 + g * 8 + 3);
-      ptx::mbar_wait(&bars->o_empty[b], (uint32_t)((n & 1) ^ 1));
+      const int t = g >> 2;
+      // the first block of a tile starts a fresh accumulator: tile t-2's output must have been read out
+      if (j == 0) ptx::mbar_wait(&bars->o_free[t & 1], (uint32_t)(((t >> 1) & 1) ^ 1));
       ptx::tcgen05_fence_after();
       constexpr uint32_t idesc = idesc_bf16(kQTile, kD, 1);
-      const uint32_t tmem_o = tmem_base + kTmemO + (uint32_t)(b * kD);
+      const uint32_t tmem_o = tmem_base + kTmemO + (uint32_t)((t & 1) * kD);
       const uint32_t tmem_p = tmem_base + kTmemS + (uint32_t)(b * kBlk);
       // A = P from TMEM: 16 keys = 8 packed columns per k-step; B = V rows j*192 + 16*kk .. +15 (2048 B = 128 desc units)
       const uint64_t db0 = dV0 + (uint64_t)(j * (kBlk * kRowBytes >> 4));
       if (j < 3) {
 #pragma unroll
         for (int kk = 0; kk < kBlk / 16; ++kk)
-          umma_bf16_ts(tmem_o, tmem_p + (uint32_t)(kk * 8), db0 + (uint64_t)(kk * 128), idesc, kk != 0);
+          umma_bf16_ts(tmem_o, tmem_p + (uint32_t)(kk * 8), db0 + (uint64_t)(kk * 128), idesc, (j != 0 || kk != 0) ? 1u : 0u);
       } else {
-        umma_bf16_ts(tmem_o, tmem_p, db0, idesc, 0u);
+        umma_bf16_ts(tmem_o, tmem_p, db0, idesc, 1u);              // tail block: never the first of a tile
       }
-      ptx::umma_commit(&bars->o_full[b]);
+      ptx::umma_commit(&bars->o_done[b]);
       if (g < 12) TR(256 + g * 8 + 4);
     };
     for (int t = 0; t < kQTiles; ++t) {
@@ -259,11 +264,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
     float* xmax = reinterpret_cast<float*>(smem + kSmemXch);          // [2 (block parity)][2 (half)][128]
     float* xsum = xmax + 2 * 2 * 128;                                 // [2 (half)][128]
     constexpr float kLog2e = 1.4426950408889634f;
-    float o[32];
     float m = -INFINITY, l = 0.f;
     for (int t = 0; t < kQTiles; ++t) {
-#pragma unroll
-      for (int i = 0; i < 32; ++i) o[i] = 0.f;
+      const uint32_t to = tmem_base + lane_base + kTmemO + (uint32_t)((t & 1) * kD + hf * 32);
       m = -INFINITY; l = 0.f;
       for (int j = 0; j < kBlocks; ++j) {
         const int g = t * kBlocks + j, b = g & 1, n = g >> 1;
@@ -301,8 +304,31 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
         // Both warps of this row group have S_j in registers past this barrier, so P_j may overwrite it.
         named_bar_sync(1 + q, 64);
         mx = fmaxf(mx, xmax[(b * 2 + (hf ^ 1)) * 128 + r]);
-        const float m_new = fmaxf(m, mx * kLog2e);                     // exp2 domain; finite
-        const float alpha = ex2(m - m_new);                            // 0 on the first block (m = -inf)
+        const float m_blk = mx * kLog2e;                               // exp2 domain; finite; same in both threads of a row
+        if (j == 0) {
+          m = m_blk;                                                   // fresh accumulator, nothing to rescale
+        } else {
+          // Lazy rescale: only when this block raises the row maximum by more than 2^8 are the accumulator and the
+          // running sum moved to the new frame; otherwise the stale maximum stays and p may reach 256.
+          const bool need = m_blk - m > 8.0f;
+          if (__any_sync(0xffffffffu, need)) {
+            const float fac = need ? ex2(m - m_blk) : 1.0f;
+            // P V of block g-1 must have retired (blocks <= g-2 have: S_g was committed after them, so this barrier is
+            // at most one phase behind and the parity wait is exact)
+            ptx::mbar_wait(&bars->o_done[(g - 1) & 1], (uint32_t)(((g - 1) >> 1) & 1));
+            ptx::tcgen05_fence_after();
+            uint32_t a[32];
+            ptx::tmem_ld_32x32b_x32(to, a);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) a[i] = __float_as_uint(__uint_as_float(a[i]) * fac);
+            tmem_st_32x32b_x16(to, a);
+            tmem_st_32x32b_x16(to + 16u, a + 16);
+            l *= fac;
+            if (need) m = m_blk;
+          }
+        }
+        const float m_new = m;
         if (trc) TR(g * 16 + 3);
         float s4[4] = {0.f, 0.f, 0.f, 0.f};
         // P_j (bf16 pairs) goes to columns [hf*48, hf*48+48) of the S_j buffer
@@ -313,8 +339,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
             uint32_t w[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-              const float p0 = ex2(fmaf(__uint_as_float(v[c][2 * i]), kLog2e, -m_new));
+              const float x0 = fmaf(__uint_as_float(v[c][2 * i]), kLog2e, -m_new);
               const float x1 = fmaf(__uint_as_float(v[c][2 * i + 1]), kLog2e, -m_new);
+              const float p0 = ex2(x0);
               const float p1 = (i & 1) ? ex2_poly(x1) : ex2(x1);
               s4[i & 3] += p0 + p1;
               w[i] = pack2(p0, p1);
@@ -337,37 +364,21 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
         ptx::tcgen05_fence_before();
         ptx::mbar_arrive(&bars->p_full[b]);
         if (trc) TR(g * 16 + 5);
-        // fold in the previous block's O (same max frame), then move to the new frame
-        if (j >= 1) {
-          const int gp = g - 1, bp = gp & 1, np = gp >> 1;
-          ptx::mbar_wait(&bars->o_full[bp], (uint32_t)(np & 1));
-          ptx::tcgen05_fence_after();
-          if (trc) TR(g * 16 + 6);
-          uint32_t vo[32];
-          ptx::tmem_ld_32x32b_x32(tmem_base + lane_base + kTmemO + (uint32_t)(bp * kD + hf * 32), vo);
-          ptx::tmem_ld_wait();
-          ptx::tcgen05_fence_before();
-          ptx::mbar_arrive(&bars->o_empty[bp]);
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o[i] += __uint_as_float(vo[i]);
-        }
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[i] *= alpha;
-        l = l * alpha + sum;
-        m = m_new;
+        l += sum;
         if (trc) TR(g * 16 + 7);
       }
-      // last block of the tile: fold its O, combine the two halves' row sums, normalise and store
+      // end of the tile: once the last P V has retired read the accumulator, combine the two halves' row sums,
+      // normalise and store
       {
-        const int g = t * kBlocks + kBlocks - 1, b = g & 1, n = g >> 1;
+        const int g = t * kBlocks + kBlocks - 1;
         xsum[hf * 128 + r] = l;
-        ptx::mbar_wait(&bars->o_full[b], (uint32_t)(n & 1));
+        ptx::mbar_wait(&bars->o_done[g & 1], (uint32_t)((g >> 1) & 1));
         ptx::tcgen05_fence_after();
         uint32_t vo[32];
-        ptx::tmem_ld_32x32b_x32(tmem_base + lane_base + kTmemO + (uint32_t)(b * kD + hf * 32), vo);
+        ptx::tmem_ld_32x32b_x32(to, vo);
         ptx::tmem_ld_wait();
         ptx::tcgen05_fence_before();
-        ptx::mbar_arrive(&bars->o_empty[b]);
+        ptx::mbar_arrive(&bars->o_free[t & 1]);
         named_bar_sync(1 + q, 64);
         const float inv = 1.0f / (l + xsum[(hf ^ 1) * 128 + r]);
         const int row = t * kQTile + r;
@@ -377,7 +388,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
           for (int c = 0; c < 4; ++c) {
             float e[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) e[i] = (o[8 * c + i] + __uint_as_float(vo[8 * c + i])) * inv;
+            for (int i = 0; i < 8; ++i) e[i] = __uint_as_float(vo[8 * c + i]) * inv;
             dst[c] = make_uint4(pack2(e[0], e[1]), pack2(e[2], e[3]), pack2(e[4], e[5]), pack2(e[6], e[7]));
           }
         }
