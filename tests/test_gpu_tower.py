@@ -257,3 +257,34 @@ def test_host_fed_stream_matches_direct_call(frontends, dev):
     for (hx, hy, hp, hoff), g in zip(batches, got):
         want = fe.visual_tokens(hx.to(dev), hy.to(dev), hp.to(dev), hoff.to(dev), (H, W)).cpu()
         assert torch.equal(g, want)
+
+
+def test_attention_lazy_rescale_and_peaked_rows(dev):
+    """The attention kernel keeps a stale row maximum unless a later key block exceeds it by more than 2^8, and then
+    rescales its TMEM accumulator in place.  Drive both paths: (a) scores that grow block after block (every block
+    rescales), (b) one dominant key in the LAST block (a single late rescale), (c) nearly constant scores (never)."""
+    from eventgpt_b200 import events as E
+    from eventgpt_b200._lib import lib, check
+    g = torch.Generator(device="cpu").manual_seed(5)
+    F = 2
+    qkv = torch.randn(F, 577, 3, 16, 64, generator=g) * 0.3
+    # (a) head 0: keys grow with their index -> every later block has a much larger maximum
+    ramp = torch.linspace(0.0, 6.0, 577)[None, :, None]
+    qkv[:, :, 1, 0] = qkv[:, :, 1, 0] + ramp * qkv[:, :1, 0, 0].sign()      # aligned with the sign pattern of row 0's q
+    qkv[:, :, 0, 0] = qkv[:, :, 0, 0].abs() * qkv[:, :1, 0, 0].sign()       # all queries share that sign pattern
+    # (b) head 1: key 570 (last block) dominates every row
+    qkv[:, :, 0, 1] = qkv[:, :, 0, 1].abs()
+    qkv[:, 570, 1, 1] = 8.0
+    # (c) head 2: tiny q -> flat softmax
+    qkv[:, :, 0, 2] *= 1e-3
+    x = qkv.reshape(F * 577, 3072).bfloat16().to(dev)
+    out = torch.empty(F * 577, 1024, device=dev, dtype=torch.bfloat16)
+    check(lib().egpt_attention(E.ptr(x), F, E.ptr(out), E.stream_ptr(dev)), "attention")
+    xf = x.float().view(F, 577, 3, 16, 64)
+    q, k, v = (xf[:, :, i].transpose(1, 2) for i in range(3))
+    s = q @ k.transpose(-1, -2)
+    assert (s[:, 0].amax(-1) - s[:, 0, :, :192].amax(-1)).max().item() > 20.0        # (a) really needs rescaling
+    ref = (torch.softmax(s, -1) @ v).transpose(1, 2).reshape(F * 577, 1024)
+    err = (out.float() - ref).abs().max().item()
+    assert torch.isfinite(out.float()).all() and err < 3e-2, err
+    assert _cos(out.float(), ref) > 0.9999
