@@ -270,6 +270,16 @@ extern "C" size_t egpt_workspace_bytes(int n_frames_total) {
   return n_frames_total > 0 ? tower_ws_bytes(n_frames_total) : 0;
 }
 
+static int check_device(const egpt_handle* h, const char* what) {
+  int dev = -1;
+  EGPT_CUDA(cudaGetDevice(&dev));
+  if (dev != h->device) {
+    set_error("%s: the handle was created on device %d but device %d is current", what, h->device, dev);
+    return EGPT_ERR_INVALID;
+  }
+  return EGPT_OK;
+}
+
 #define EGPT_WS_OR_FAIL(F)                                                                       \
   TowerWs w;                                                                                     \
   if (!carve_tower_ws(workspace, workspace_bytes, (F), &w)) {                                    \
@@ -281,6 +291,7 @@ extern "C" int egpt_tower(egpt_handle* h, const uint16_t* pixel_values, int F, u
                           size_t workspace_bytes, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   EGPT_CHECK_ARG(h && pixel_values && out_hidden && workspace && F > 0, "egpt_tower: bad arguments");
+  EGPT_TRY(check_device(h, "egpt_tower"));
   EGPT_WS_OR_FAIL(F);
   EGPT_TRY(im2col(pixel_values, w.qkv, F, st));
   EGPT_TRY(run_tower_from_patches(h, F, w, st));
@@ -292,6 +303,7 @@ extern "C" int egpt_visval_encode(egpt_handle* h, const uint16_t* pixel_values, 
                                   void* workspace, size_t workspace_bytes, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   EGPT_CHECK_ARG(h && pixel_values && out_features && workspace && F > 0, "egpt_visval_encode: bad arguments");
+  EGPT_TRY(check_device(h, "egpt_visval_encode"));
   EGPT_WS_OR_FAIL(F);
   EGPT_TRY(im2col(pixel_values, w.qkv, F, st));
   EGPT_TRY(run_tower_from_patches(h, F, w, st));
@@ -301,6 +313,7 @@ extern "C" int egpt_visval_encode(egpt_handle* h, const uint16_t* pixel_values, 
 
 extern "C" int egpt_feature_adaptor(egpt_handle* h, const uint16_t* in, int64_t rows, uint16_t* out, void* stream) {
   EGPT_CHECK_ARG(h && in && out && rows > 0, "egpt_feature_adaptor: bad arguments");
+  EGPT_TRY(check_device(h, "egpt_feature_adaptor"));
   return gemm_bf16(in, h->adaptor_w, h->adaptor_b, out, rows, kLlm, kLlm, EPI_BIAS_BF16, (cudaStream_t)stream);
 }
 
@@ -309,6 +322,7 @@ extern "C" int egpt_encode_pool(egpt_handle* h, const uint16_t* pixel_values, in
   cudaStream_t st = (cudaStream_t)stream;
   EGPT_CHECK_ARG(h && pixel_values && out_tokens && workspace && n_windows > 0 && n_frames > 0 && n_frames <= 8,
                  "egpt_encode_pool: bad arguments (n_frames must be 1..8)");
+  EGPT_TRY(check_device(h, "egpt_encode_pool"));
   const int F = n_windows * n_frames;
   EGPT_WS_OR_FAIL(F);
   EGPT_TRY(im2col(pixel_values, w.qkv, F, st));
@@ -335,6 +349,7 @@ extern "C" int egpt_visual_tokens(egpt_handle* h, const void* x, const void* y, 
   EGPT_CHECK_ARG(h && x && y && p && window_offsets && out_tokens && out_hw && status && workspace,
                  "egpt_visual_tokens: null pointer argument");
   EGPT_CHECK_ARG(n_windows > 0 && n_frames > 0 && n_frames <= 8 && H > 0 && W > 0, "egpt_visual_tokens: bad shape");
+  EGPT_TRY(check_device(h, "egpt_visual_tokens"));
   if (workspace_bytes < egpt_visual_tokens_workspace_bytes(n_windows, n_frames, H, W)) {
     set_error("egpt_visual_tokens: workspace %zu < %zu bytes", workspace_bytes,
               egpt_visual_tokens_workspace_bytes(n_windows, n_frames, H, W));

@@ -446,12 +446,8 @@ int attention_impl(const void* qkv, int n_frames_total, void* out, cudaStream_t 
          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_error("attention: cuTensorMapEncodeTiled (tail) failed with CUresult %d", (int)r); return EGPT_ERR_CUDA; }
-  static std::once_flag once;
-  cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal);
-  });
-  EGPT_CUDA(attr_err);
+  // per launch: the attribute is per device, and one process may drive several GPUs
+  EGPT_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
   ProfScope prof(PROF_ATTN, 4.0 * kS * kS * kD * kHeads * (double)n_frames_total, stream);
   attention_tc_kernel<<<n_frames_total * kHeads, kThreads, kSmemTotal, stream>>>(tm, tm_tail, reinterpret_cast<__nv_bfloat16*>(out), trace);
   EGPT_LAUNCH_CHECK();

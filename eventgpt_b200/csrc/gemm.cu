@@ -255,12 +255,8 @@ static int make_tmap(CUtensorMap* map, const void* ptr, bool f32, uint64_t rows,
 template <int EPI>
 static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const float* bias,
                         long long M, int N, int K, cudaStream_t stream) {
-  static std::once_flag once;
-  cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(gemm2_bf16_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem2);
-  });
-  EGPT_CUDA(attr_err);
+  // per launch: the attribute is per device, and one process may drive several GPUs
+  EGPT_CUDA(cudaFuncSetAttribute(gemm2_bf16_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem2));
   const long long pairs = ((M + 2 * BM - 1) / (2 * BM)) * (N / BN);
   const int grid = (int)(2 * (pairs < kNumSMs / 2 ? pairs : kNumSMs / 2));
   gemm2_bf16_kernel<EPI><<<grid, kGemmThreads, kGemmSmem2, stream>>>(ta, tb, to, bias, M, N, K);
