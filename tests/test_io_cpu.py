@@ -1,0 +1,54 @@
+"""dataset/io.py:38-87 mirrors on an in-memory DSEC-layout recording: the same slices as a
+direct restatement of the reference arithmetic, and consistency of the window-offset helper."""
+import math
+
+import numpy as np
+import pytest
+
+from eventgpt_b200 import io as eio
+
+
+def make_recording(seed=0, n=200_000, dur_ms=400):
+    rng = np.random.default_rng(seed)
+    t = np.sort(rng.integers(0, dur_ms * 1000, n)).astype(np.uint32)
+    ms_to_idx = np.searchsorted(t, np.arange(dur_ms + 1) * 1000, side="left").astype(np.uint64)   # DSEC convention
+    return {"events": {"x": rng.integers(0, 640, n).astype(np.uint16), "y": rng.integers(0, 480, n).astype(np.uint16),
+                       "p": rng.integers(0, 2, n).astype(np.uint8), "t": t},
+            "ms_to_idx": ms_to_idx, "t_offset": np.int64(51_000_000_000)}
+
+
+def reference_timewindow(f, t_min_us, t_max_us):
+    """literal restatement of dataset/io.py:68-87"""
+    ms2idx = np.asarray(f["ms_to_idx"], dtype="int64")
+    t_offset = f["t_offset"][()]
+    t = f["events"]["t"]
+    s = ms2idx[(t_min_us - t_offset) // 1000]
+    t_end = t_max_us - t_offset
+    assert t_end <= t[-1]
+    e = ms2idx[math.floor(t_end / 1000)]
+    return {k: (f["events"][k][s:e].astype("int64") + t_offset if k == "t" else f["events"][k][s:e]) for k in "ptxy"}
+
+
+def test_timewindow_matches_reference_arithmetic():
+    f = make_recording()
+    off = int(f["t_offset"])
+    for (a, b) in [(0, 50_000), (50_000, 100_000), (123_456, 299_999), (0, 1_000)]:
+        got = eio.extract_from_h5_by_timewindow(f, off + a, off + b)
+        want = reference_timewindow(f, off + a, off + b)
+        for k in "ptxy":
+            assert got[k].dtype == want[k].dtype and np.array_equal(got[k], want[k])
+        assert got["t"].dtype == np.int64
+    with pytest.raises(AssertionError):
+        eio.extract_from_h5_by_timewindow(f, off, off + 10_000_000)
+
+
+def test_window_offsets_feed_the_rasteriser_layout():
+    f = make_recording(1)
+    offs = eio.window_offsets_from_ms_index(f["ms_to_idx"], 50)
+    assert len(offs) == 9 and offs[0] == 0 and np.all(np.diff(offs) >= 0)
+    t = f["events"]["t"]
+    for i in range(8):
+        w = t[offs[i]:offs[i + 1]]
+        assert w.size == 0 or (w.min() >= i * 50_000 and w.max() < (i + 1) * 50_000)
+        sl = eio.extract_from_h5_by_index(f, offs[i], offs[i + 1])
+        assert len(sl["t"]) == offs[i + 1] - offs[i] and eio.get_num_events(f) == 200_000
