@@ -3,24 +3,27 @@
 // called from model/EventChatModel.py:196).  Input: packed QKV projection [F*577, 3072] bf16
 // (q pre-scaled by 1/8 in the weights); output bf16 [F*577, 1024].
 //
-// One CTA per (frame, head), 384 threads:
-//   warp 8     TMA producer: K and V of the head (592 padded rows x 64, zero filled past 577 by the
-//              3-D tensor map) once, then one 128-row Q tile at a time
-//   warp 9     MMA issuer (one thread): S_j = Q K_j^T (M128 x N192 x K64) into a double-buffered TMEM
-//              region, then O_j = P_j V_j (M128 x N64 x K192; P read straight from TMEM where the
-//              softmax warps wrote it over S_j, V from shared memory as an MN-major operand)
-//   warp 10    TMEM allocator (512 columns: 2 x 192 for S, 2 x 64 for the output of even / odd tiles)
-//   warps 0-7  softmax: two threads per query row, each owning half of the key columns of a block
-//              and half of the 64 output dims.  S_j is read from TMEM once into registers, the
-//              row maximum is exchanged with the partner thread through shared memory, P_j goes
-//              back into the same TMEM columns as packed bf16 (tcgen05.st).  The output accumulates
-//              in TMEM across the key blocks of a tile; it is rescaled in place only when a block
-//              raises a row's maximum by more than 2^8 (otherwise the stale maximum is kept: p <= 256
-//              is harmless in fp32 / bf16), so the common path is load S, max, exp2, store P.
-// Keys are walked in four blocks of 192, 192, 192 and 16 (= 592 >= 577).
+// One CTA per (frame, head), 384 threads.  The 577 keys are split into two key groups of 288 (three blocks of
+// 96) plus one left-over key; each group is an independent flash-attention pipeline over the same 128-row Q
+// tile, and the two partial results of a row are merged once per tile:
+//   warps 0-3 / 4-7  softmax of key group 0 / 1: one thread per (row, group).  S_n is read from TMEM into
+//              registers, P_n = exp2(S_n - m) goes back over it as packed bf16 (tcgen05.st), the group's partial
+//              output accumulates in TMEM across the three blocks and is rescaled in place only when a block
+//              raises the row maximum by more than 2^8 (otherwise the stale maximum is kept: p <= 256 is harmless
+//              in fp32 / bf16).  A quarter of the exp2 runs as a cubic on the FMA pipe.  The merge of tile t
+//              (two partial outputs + the left-over key, which is handled on the CUDA cores: a 64-long dot
+//              product per row) is deferred until the first block of tile t+1 has been handed to the tensor
+//              pipe, so no softmax warp ever waits for a P V product to retire.
+//   warp 8     TMA producer: K and V of the head (592 padded rows x 64, zero filled past 577 by the 3-D
+//              tensor map) once, then 128-row Q tiles into a double buffer
+//   warps 9/11 MMA issuer of group 0 / 1 (one thread each): S_n = Q K_n^T (M128 x N96 x K64, SS) into a double
+//              buffer, O_g += P_n V_n (TS form: P read from TMEM, V from shared memory as an MN-major operand)
+//   warp 10    TMEM allocator (2 groups x 2 x 96 columns for S / P, 2 x 64 for the partial outputs)
+// The control warps sit in the highest warp ids: the warp arbiter favours them, and the single-thread issuers
+// must not starve for issue slots behind eight busy softmax warps.  Registers are handed from the control
+// warps to the softmax warps with setmaxnreg.
 #include "common.cuh"
 #include "sm100_ptx.cuh"
-#include <mutex>
 
 namespace egpt {
 
@@ -31,21 +34,24 @@ constexpr int kHeads = 16;
 constexpr int kKeyPad = 592;
 constexpr int kQTile = 128;
 constexpr int kQTiles = (kS + kQTile - 1) / kQTile;      // 5
-constexpr int kBlocks = 4;                                // key blocks per q tile: 192,192,192,16
-constexpr int kBlk = 192;
-constexpr int kTail = kKeyPad - 3 * kBlk;                 // 16
+constexpr int kBlk = 96;                                  // keys per block
+constexpr int kGroupKeys = 3 * kBlk;                      // 288: key group 0 = keys [0,288), group 1 = [288,592)
+constexpr int kXKey = 2 * kGroupKeys;                     // 576: the left-over key, handled outside the MMAs
+constexpr int kNBlk = 3;                                  // blocks per group and tile
 constexpr int kThreads = 384;
 constexpr int kRowBytes = 128;                            // 64 bf16
 constexpr int kKVBytes = kKeyPad * kRowBytes;             // 75776
 constexpr int kQBytes = kQTile * kRowBytes;               // 16384
 constexpr int kSmemK = 0, kSmemV = kKVBytes, kSmemQ = 2 * kKVBytes;
-constexpr int kSmemBar = kSmemQ + kQBytes;                // 167936
-constexpr int kSmemXch = kSmemBar + 256;                  // float [2][2][128] row maxima + [2][128] row sums
-constexpr int kSmemTotal = kSmemXch + 3 * 1024 + 1024;    // + alignment slack
+constexpr int kSmemBar = kSmemQ + 2 * kQBytes;
+constexpr int kSmemXch = kSmemBar + 512;                  // float [3 (max, sum, partial dot)][2 (tile parity)][2 (group)][128]
+constexpr int kSmemStage = kSmemXch + 6 * 1024;           // output staging: 8 warps x (32 rows x 64 B)
+constexpr int kStageBytes = 32 * 64;
+constexpr int kSmemTotal = kSmemStage + 8 * kStageBytes + 1024;   // + alignment slack
+constexpr int kStagger = 900;                             // cycles by which key group 1 starts behind group 0
 constexpr int kTmemCols = 512;
-constexpr uint32_t kTmemS = 0, kTmemO = 2 * kBlk;         // columns
-
-__device__ __forceinline__ int block_cols(int j) { return j < 3 ? kBlk : kTail; }   // 192 / 16
+constexpr uint32_t kTmemS = 0, kTmemO = 4 * kBlk;         // columns: S/P [group][buffer][96], then O [group][64]
+constexpr int kPolyEvery = 4;                             // every kPolyEvery-th pair of exp2 runs as a cubic on the FMA pipe (0: none)
 
 // MN-major B operand (V block: rows = keys (K), 64 contiguous dims (N) = 128 B per key, SWIZZLE_128B):
 // 8-key groups are 1024 B apart (SBO); a single 64-wide N block, so LBO is unused.
@@ -70,14 +76,17 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m
       ::"r"(ptx::smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(ptx::smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(ptx::smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
 __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-// 2^x for x <= 0 on the FMA/ALU pipes (Cody-Waite split + cubic), used for a quarter of the
-// elements so the MUFU pipe (16 exp2/clk/SM, the unit this kernel saturates) is not the only
-// exponential engine.  Relative error < 1e-4, far below the bf16 rounding P undergoes anyway.
+// 2^x for x <= ~8 on the FMA/ALU pipes (Cody-Waite split + cubic).  Relative error < 1e-4, far below the bf16
+// rounding P undergoes anyway.
 __device__ __forceinline__ float ex2_poly(float x) {
   x = fmaxf(x, -126.0f);
   const float t = x + 12582912.0f;                 // 1.5 * 2^23: rounds x to the nearest integer n
@@ -88,19 +97,36 @@ __device__ __forceinline__ float ex2_poly(float x) {
   p = fmaf(p, f, 1.0f);
   return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
 }
+// packed fp32x2 arithmetic (sm_100): one issue slot for two lanes of fma / add
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  float2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(*reinterpret_cast<unsigned long long*>(&d))
+      : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)),
+        "l"(*reinterpret_cast<unsigned long long*>(&c)));
+  return d;
+}
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+  float2 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(*reinterpret_cast<unsigned long long*>(&d))
+      : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)));
+  return d;
+}
+// two cubic exp2 at once (same scheme as ex2_poly)
+__device__ __forceinline__ float2 ex2_poly2(float2 x) {
+  x.x = fmaxf(x.x, -126.0f); x.y = fmaxf(x.y, -126.0f);
+  const float2 t = fadd2(x, make_float2(12582912.0f, 12582912.0f));
+  const float2 n = fadd2(t, make_float2(-12582912.0f, -12582912.0f));
+  const float2 f = ffma2(n, make_float2(-1.f, -1.f), x);
+  float2 p = ffma2(f, make_float2(0.0555041f, 0.0555041f), make_float2(0.2402265f, 0.2402265f));
+  p = ffma2(p, f, make_float2(0.6931472f, 0.6931472f));
+  p = ffma2(p, f, make_float2(1.0f, 1.0f));
+  p.x = __int_as_float(__float_as_int(p.x) + (__float_as_int(t.x) << 23));
+  p.y = __int_as_float(__float_as_int(p.y) + (__float_as_int(t.y) << 23));
+  return p;
+}
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
-}
-
-__device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&r)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr)
-      : "memory");
 }
 __device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t* r) {
   asm volatile(
@@ -128,18 +154,30 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 }
 
 struct Bars {
-  uint64_t k_full[kBlocks], v_full[kBlocks];
-  uint64_t q_full, q_empty;
-  uint64_t s_full[2];
-  uint64_t p_full[2];
-  uint64_t o_done[2];                    // [block parity]: the P V product of a block has retired
-  uint64_t o_free[2];                    // [tile parity]: the tile's output was read out of TMEM
+  uint64_t k_full[2][kNBlk], v_full[2][kNBlk];
+  uint64_t x_full;                       // rows 576..591 of K and V (the left-over key + zero fill)
+  uint64_t q_full[2], q_empty[2];        // Q tile double buffer; q_empty counts both issuers
+  uint64_t s_full[2][2];                 // [group][buffer]: S block landed
+  uint64_t p_full[2][2];                 // [group][buffer]: P stored over it by the group's 128 threads
+  uint64_t o_done[2][2];                 // [group][block parity]: P V of a block retired
+  uint64_t o_free;                       // the tile's two partial outputs were read out by all 256 threads
+  uint64_t x_ready[2];                   // [group]: the group's (max, sum, dot) of a finished tile are in shared memory
   uint32_t tmem_ptr;
 };
 
+// 8 bf16 (one 16-byte chunk of a SWIZZLE_128B row) -> fp32
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    f[2 * i] = __uint_as_float(w[i] << 16);
+    f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+
 __global__ void __launch_bounds__(kThreads, 1)
-attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_tail,
-                    __nv_bfloat16* __restrict__ out, long long* __restrict__ trace) {
+attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
+                    const __grid_constant__ CUtensorMap tmap_out, long long* __restrict__ trace) {
   extern __shared__ uint8_t smem_raw[];
 #ifdef EGPT_ATTN_TRACE   // developer aid: clock64 phase stamps of CTA 0 (tools/attn_trace.py)
 #define TR(slot) do { if (trace != nullptr && blockIdx.x == 0) trace[(slot)] = clock64(); } while (0)
@@ -151,14 +189,18 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int f = blockIdx.x / kHeads, h = blockIdx.x % kHeads;
 
-  if (warp == 8 && lane == 0) { ptx::prefetch_tensormap(&tmap_qkv); ptx::prefetch_tensormap(&tmap_tail); }
+  if (warp == 8 && lane == 0) { ptx::prefetch_tensormap(&tmap_q); ptx::prefetch_tensormap(&tmap_kv); ptx::prefetch_tensormap(&tmap_out); }
   if (warp == 9 && lane == 0) {
-    for (int i = 0; i < kBlocks; ++i) { ptx::mbar_init(&bars->k_full[i], 1); ptx::mbar_init(&bars->v_full[i], 1); }
-    ptx::mbar_init(&bars->q_full, 1); ptx::mbar_init(&bars->q_empty, 1);
-    for (int i = 0; i < 2; ++i) {
-      ptx::mbar_init(&bars->s_full[i], 1); ptx::mbar_init(&bars->p_full[i], 256);
-      ptx::mbar_init(&bars->o_done[i], 1); ptx::mbar_init(&bars->o_free[i], 256);
+    for (int g = 0; g < 2; ++g) {
+      for (int i = 0; i < kNBlk; ++i) { ptx::mbar_init(&bars->k_full[g][i], 1); ptx::mbar_init(&bars->v_full[g][i], 1); }
+      ptx::mbar_init(&bars->q_full[g], 1); ptx::mbar_init(&bars->q_empty[g], 2);
+      ptx::mbar_init(&bars->x_ready[g], 128);
+      for (int i = 0; i < 2; ++i) {
+        ptx::mbar_init(&bars->s_full[g][i], 1); ptx::mbar_init(&bars->p_full[g][i], 128); ptx::mbar_init(&bars->o_done[g][i], 1);
+      }
     }
+    ptx::mbar_init(&bars->x_full, 1);
+    ptx::mbar_init(&bars->o_free, 256);
     ptx::fence_barrier_init();
   }
   if (warp == 10) {
@@ -169,232 +211,277 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
   __syncthreads();
   ptx::tcgen05_fence_after();
   const uint32_t tmem_base = bars->tmem_ptr;
-  // hand registers from the four control warps to the softmax warps (the row block lives in registers)
-  // Softmax warps are 0-7, control warps 8-11: the warp arbiter favours higher warp ids and the single-thread
-  // TMA / MMA issuers must not starve for issue slots behind eight busy softmax warps.
+
   if (warp >= 8) {
-  asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
-  if (warp == 8 && lane == 0) {
-    // ===== TMA producer =====
-    // Q tile 0 first, then K and V block by block (64-row boxes) so the first MMAs can start early
-    ptx::mbar_arrive_expect_tx(&bars->q_full, kQBytes);
-    tma_load_3d(smem + kSmemQ, &tmap_qkv, &bars->q_full, h * kD, 0, f);
-    tma_load_3d(smem + kSmemQ + 64 * kRowBytes, &tmap_qkv, &bars->q_full, h * kD, 64, f);
-    for (int kv = 0; kv < 2; ++kv) {
-      uint8_t* dst = smem + (kv == 0 ? kSmemK : kSmemV);
-      uint64_t* full = kv == 0 ? bars->k_full : bars->v_full;
-      const int col = (kv + 1) * kHeads * kD + h * kD;
-      for (int j = 0; j < kBlocks; ++j) {
-        const int rows = block_cols(j);
-        ptx::mbar_arrive_expect_tx(&full[j], rows * kRowBytes);
-        if (j < 3) {
-          for (int r = 0; r < rows; r += 64)
-            tma_load_3d(dst + (j * kBlk + r) * kRowBytes, &tmap_qkv, &full[j], col, j * kBlk + r, f);
-        } else {
-          tma_load_3d(dst + 3 * kBlk * kRowBytes, &tmap_tail, &full[j], col, 3 * kBlk, f);      // 16-row box
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+    if (warp == 8 && lane == 0) {
+      // ===== TMA producer =====
+      auto load_q = [&](int t) {
+        uint8_t* dst = smem + kSmemQ + (t & 1) * kQBytes;
+        ptx::mbar_arrive_expect_tx(&bars->q_full[t & 1], kQBytes);
+        tma_load_3d(dst, &tmap_q, &bars->q_full[t & 1], h * kD, t * kQTile, f);
+        tma_load_3d(dst + 64 * kRowBytes, &tmap_q, &bars->q_full[t & 1], h * kD, t * kQTile + 64, f);
+      };
+      load_q(0);
+      // K then V, block by block and alternating between the two key groups (16-row boxes), so both groups' first
+      // MMAs can start before everything has landed
+      for (int kv = 0; kv < 2; ++kv) {
+        uint8_t* dst = smem + (kv == 0 ? kSmemK : kSmemV);
+        const int col = (kv + 1) * kHeads * kD + h * kD;
+        for (int j = 0; j < kNBlk; ++j)
+          for (int g = 0; g < 2; ++g) {
+            uint64_t* full = kv == 0 ? &bars->k_full[g][j] : &bars->v_full[g][j];
+            const int row0 = g * kGroupKeys + j * kBlk;
+            ptx::mbar_arrive_expect_tx(full, kBlk * kRowBytes);
+            for (int r = 0; r < kBlk; r += 16) tma_load_3d(dst + (row0 + r) * kRowBytes, &tmap_kv, full, col, row0 + r, f);
+          }
+        if (kv == 0) {
+          load_q(1);
+          ptx::mbar_arrive_expect_tx(&bars->x_full, 2 * 16 * kRowBytes);
+          tma_load_3d(smem + kSmemK + kXKey * kRowBytes, &tmap_kv, &bars->x_full, kHeads * kD + h * kD, kXKey, f);
+          tma_load_3d(smem + kSmemV + kXKey * kRowBytes, &tmap_kv, &bars->x_full, 2 * kHeads * kD + h * kD, kXKey, f);
         }
       }
-    }
-    for (int t = 1; t < kQTiles; ++t) {
-      ptx::mbar_wait(&bars->q_empty, (uint32_t)((t - 1) & 1));       // tile t-1's last Q K^T has retired
-      ptx::mbar_arrive_expect_tx(&bars->q_full, kQBytes);
-      // two 64-row boxes: the tensor map's box is 64 rows
-      tma_load_3d(smem + kSmemQ, &tmap_qkv, &bars->q_full, h * kD, t * kQTile, f);
-      tma_load_3d(smem + kSmemQ + 64 * kRowBytes, &tmap_qkv, &bars->q_full, h * kD, t * kQTile + 64, f);
-    }
-  } else if (warp == 9 && lane == 0) {
-    // ===== MMA issuer =====
-    const uint32_t sK = ptx::smem_u32(smem + kSmemK), sV = ptx::smem_u32(smem + kSmemV);
-    const uint32_t sQ = ptx::smem_u32(smem + kSmemQ);
-    const uint64_t dV0 = make_desc_mn_sw128(sV), dK0 = ptx::make_smem_desc_sw128(sK), dQ = ptx::make_smem_desc_sw128(sQ);
-    auto issue_pv = [&](int g) {
-      const int j = g & 3, b = g & 1, n = g >> 1;
-      if (g < kBlocks) ptx::mbar_wait(&bars->v_full[j], 0);
-      if (g < 12) TR(256 + g * 8 + 2);
-      ptx::mbar_wait(&bars->p_full[b], (uint32_t)(n & 1));
-      if (g < 12) TR(256 + g * 8 + 3);
-      const int t = g >> 2;
-      // the first block of a tile starts a fresh accumulator: tile t-2's output must have been read out
-      if (j == 0) ptx::mbar_wait(&bars->o_free[t & 1], (uint32_t)(((t >> 1) & 1) ^ 1));
-      ptx::tcgen05_fence_after();
-      constexpr uint32_t idesc = idesc_bf16(kQTile, kD, 1);
-      const uint32_t tmem_o = tmem_base + kTmemO + (uint32_t)((t & 1) * kD);
-      const uint32_t tmem_p = tmem_base + kTmemS + (uint32_t)(b * kBlk);
-      // A = P from TMEM: 16 keys = 8 packed columns per k-step; B = V rows j*192 + 16*kk .. +15 (2048 B = 128 desc units)
-      const uint64_t db0 = dV0 + (uint64_t)(j * (kBlk * kRowBytes >> 4));
-      if (j < 3) {
+      for (int t = 2; t < kQTiles; ++t) {
+        ptx::mbar_wait(&bars->q_empty[t & 1], (uint32_t)(((t >> 1) - 1) & 1));   // both groups' last Q K^T of tile t-2 retired
+        load_q(t);
+      }
+    } else if ((warp == 9 || warp == 11) && lane == 0) {
+      // ===== MMA issuer of key group gi: an independent in-order stream of S and P V products =====
+      const int gi = warp == 9 ? 0 : 1;
+      const uint64_t dK0 = ptx::make_smem_desc_sw128(ptx::smem_u32(smem + kSmemK + gi * kGroupKeys * kRowBytes));
+      const uint64_t dV0 = make_desc_mn_sw128(ptx::smem_u32(smem + kSmemV + gi * kGroupKeys * kRowBytes));
+      const uint64_t dQ0 = ptx::make_smem_desc_sw128(ptx::smem_u32(smem + kSmemQ));
+      const uint32_t tmem_s0 = tmem_base + kTmemS + (uint32_t)(gi * 2 * kBlk);
+      const uint32_t tmem_o = tmem_base + kTmemO + (uint32_t)(gi * kD);
+      constexpr uint32_t idesc_pv = idesc_bf16(kQTile, kD, 1);
+      constexpr uint32_t idesc_s = idesc_bf16(kQTile, kBlk, 0);
+      auto issue_pv = [&](int n) {
+        const int t = n / kNBlk, j = n - t * kNBlk, b = n & 1;
+        if (n < kNBlk) ptx::mbar_wait(&bars->v_full[gi][j], 0);
+        TR(1024 + gi * 256 + n * 8 + 2);
+        ptx::mbar_wait(&bars->p_full[gi][b], (uint32_t)((n >> 1) & 1));
+        TR(1024 + gi * 256 + n * 8 + 3);
+        // the first block of a tile overwrites the accumulator: the previous tile's output must have been read out
+        if (j == 0 && t > 0) ptx::mbar_wait(&bars->o_free, (uint32_t)((t - 1) & 1));
+        ptx::tcgen05_fence_after();
+        const uint32_t tmem_p = tmem_s0 + (uint32_t)(b * kBlk);
+        // A = P from TMEM: 16 keys = 8 packed columns per k-step; B = V rows 16*kk .. +15 of the block (2048 B = 128 units)
+        const uint64_t dv = dV0 + (uint64_t)(j * (kBlk * kRowBytes >> 4));
 #pragma unroll
         for (int kk = 0; kk < kBlk / 16; ++kk)
-          umma_bf16_ts(tmem_o, tmem_p + (uint32_t)(kk * 8), db0 + (uint64_t)(kk * 128), idesc, (j != 0 || kk != 0) ? 1u : 0u);
-      } else {
-        umma_bf16_ts(tmem_o, tmem_p, db0, idesc, 1u);              // tail block: never the first of a tile
-      }
-      ptx::umma_commit(&bars->o_done[b]);
-      if (g < 12) TR(256 + g * 8 + 4);
-    };
-    for (int t = 0; t < kQTiles; ++t) {
-      ptx::mbar_wait(&bars->q_full, (uint32_t)(t & 1));
-      for (int j = 0; j < kBlocks; ++j) {
-        const int g = t * kBlocks + j, b = g & 1;
-        if (g < 12) TR(256 + g * 8 + 0);
-        if (t == 0) ptx::mbar_wait(&bars->k_full[j], 0);
-        // S_g overwrites the buffer that held S_{g-2} / P_{g-2}: the tensor pipe runs MMAs in issue order,
-        // and P V of block g-2 was issued before this point, so no barrier is needed for that reuse.
-        ptx::tcgen05_fence_after();
-        const uint32_t idesc = j < 3 ? idesc_bf16(kQTile, kBlk, 0) : idesc_bf16(kQTile, kTail, 0);
-        const uint32_t tmem_s = tmem_base + kTmemS + (uint32_t)(b * kBlk);
-        const uint64_t db = dK0 + (uint64_t)(j * (kBlk * kRowBytes >> 4));
+          umma_bf16_ts(tmem_o, tmem_p + (uint32_t)(kk * 8), dv + (uint64_t)(kk * 128), idesc_pv, (j != 0 || kk != 0) ? 1u : 0u);
+        ptx::umma_commit(&bars->o_done[gi][b]);
+        TR(1024 + gi * 256 + n * 8 + 4);
+      };
+      int n = 0;
+      for (int t = 0; t < kQTiles; ++t) {
+        ptx::mbar_wait(&bars->q_full[t & 1], (uint32_t)((t >> 1) & 1));
+        const uint64_t dq = dQ0 + (uint64_t)((t & 1) * (kQBytes >> 4));
+        for (int j = 0; j < kNBlk; ++j, ++n) {
+          if (t == 0) ptx::mbar_wait(&bars->k_full[gi][j], 0);
+          TR(1024 + gi * 256 + n * 8 + 0);
+          // S_n overwrites the buffer that held P_{n-2}; P V of block n-2 was issued earlier by this same thread and
+          // the tensor pipe runs one thread's MMAs in issue order, so that reuse needs no barrier.
+          ptx::tcgen05_fence_after();
+          const uint32_t tmem_s = tmem_s0 + (uint32_t)((n & 1) * kBlk);
+          const uint64_t dk = dK0 + (uint64_t)(j * (kBlk * kRowBytes >> 4));
 #pragma unroll
-        for (int k = 0; k < kD / 16; ++k) ptx::umma_bf16_ss(tmem_s, dQ + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, k != 0);
-        ptx::umma_commit(&bars->s_full[b]);
-        if (g < 12) TR(256 + g * 8 + 1);
-        if (j == kBlocks - 1) ptx::umma_commit(&bars->q_empty);
-        if (g >= 1) issue_pv(g - 1);
+          for (int k = 0; k < kD / 16; ++k) ptx::umma_bf16_ss(tmem_s, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc_s, k != 0);
+          ptx::umma_commit(&bars->s_full[gi][n & 1]);
+          TR(1024 + gi * 256 + n * 8 + 1);
+          if (j == kNBlk - 1) ptx::umma_commit(&bars->q_empty[t & 1]);
+          if (n >= 1) issue_pv(n - 1);
+        }
       }
+      issue_pv(n - 1);
     }
-    issue_pv(kQTiles * kBlocks - 1);
-  }
   } else {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
-    // ===== softmax: thread (row r, half hf) owns key columns [hf*96, hf*96+96) of a 192-key block
-    // (the 16-key tail block belongs to half 0) and output dims [hf*32, hf*32+32) =====
-    const int q = warp & 3, hf = warp >> 2;
+    // ===== softmax: thread (row r, key group gi) walks its group's key blocks on its own: own running maximum, own
+    // row sum, own partial output in TMEM =====
+    const int q = warp & 3, gi = warp >> 2;
     const int r = q * 32 + lane;                       // row inside the tile == TMEM lane
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
-    float* xmax = reinterpret_cast<float*>(smem + kSmemXch);          // [2 (block parity)][2 (half)][128]
-    float* xsum = xmax + 2 * 2 * 128;                                 // [2 (half)][128]
+    const uint32_t tmem_s0 = tmem_base + lane_base + kTmemS + (uint32_t)(gi * 2 * kBlk);
+    const uint32_t tmem_o = tmem_base + lane_base + kTmemO + (uint32_t)(gi * kD);
+    const uint32_t tmem_o_other = tmem_base + lane_base + kTmemO + (uint32_t)((gi ^ 1) * kD);
+    float* xch = reinterpret_cast<float*>(smem + kSmemXch);           // [3][2 (tile parity)][2 (group)][128]
     constexpr float kLog2e = 1.4426950408889634f;
+    const bool trc = (q == 0 && lane == 0);
     float m = -INFINITY, l = 0.f;
+    float dot_cur = 0.f;                                               // this thread's half of q_r . k_576 for the tile
+
+    // Merge of tile tp: the two groups' (max, sum, partial output) and the left-over key 576, whose score is the sum of
+    // the two threads' partial dot products.  Each thread finishes 32 of the 64 output dims.
+    auto publish = [&](int tp) {                                       // at the end of the tile's last block
+      float* x_t = xch + (tp & 1) * 256;
+      x_t[gi * 128 + r] = m;
+      x_t[512 + gi * 128 + r] = l;
+      x_t[1024 + gi * 128 + r] = dot_cur;
+      ptx::mbar_arrive(&bars->x_ready[gi]);
+    };
+    auto merge = [&](int tp) {
+      const int last = tp * kNBlk + kNBlk - 1;
+      const float* x_t = xch + (tp & 1) * 256;
+      const float m_me = x_t[gi * 128 + r], l_me = x_t[512 + gi * 128 + r];
+      // The partner group runs on its own clock.  Its numbers for tile tp and its last P V of that tile: both barriers are
+      // at most one phase behind here (the partner cannot finish tile tp+1 before this thread has released o_free).
+      ptx::mbar_wait(&bars->x_ready[gi ^ 1], (uint32_t)(tp & 1));
+      const float mo = x_t[(gi ^ 1) * 128 + r], lo = x_t[512 + (gi ^ 1) * 128 + r];
+      const float sx = (x_t[1024 + gi * 128 + r] + x_t[1024 + (gi ^ 1) * 128 + r]) * kLog2e;
+      ptx::mbar_wait(&bars->o_done[gi][last & 1], (uint32_t)((last >> 1) & 1));
+      ptx::mbar_wait(&bars->o_done[gi ^ 1][last & 1], (uint32_t)((last >> 1) & 1));
+      if (trc) TR(gi * 512 + last * 16 + 7);
+      ptx::tcgen05_fence_after();
+      uint32_t oa[32], ob[32];
+      ptx::tmem_ld_32x32b_x32(tmem_o + (uint32_t)(gi * 32), oa);
+      ptx::tmem_ld_32x32b_x32(tmem_o_other + (uint32_t)(gi * 32), ob);
+      ptx::tmem_ld_wait();
+      ptx::tcgen05_fence_before();
+      ptx::mbar_arrive(&bars->o_free);
+      if (trc) TR(gi * 512 + last * 16 + 8);
+      const float mt = fmaxf(fmaxf(m_me, mo), sx);
+      const float fa = ex2(m_me - mt), fb = ex2(mo - mt), px = ex2(sx - mt);
+      const float inv = __fdividef(1.0f, fmaf(l_me, fa, lo * fb) + px);
+      const float ca = fa * inv, cb = fb * inv, cx = px * inv;
+      // 32 rows x 32 dims of this warp go out as one TMA store (rows past 577 are clipped by the tensor map)
+      uint8_t* stage = smem + kSmemStage + warp * kStageBytes;
+      if (lane == 0) ptx::bulk_wait_group_read<0>();                   // the previous tile's store has read the slab
+      __syncwarp();
+      const uint4* vx = reinterpret_cast<const uint4*>(smem + kSmemV + kXKey * kRowBytes) + gi * 4;   // row 576: unswizzled
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        float e[8], vf[8];
+        unpack8(vx[c], vf);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          e[i] = fmaf(__uint_as_float(oa[8 * c + i]), ca, fmaf(__uint_as_float(ob[8 * c + i]), cb, vf[i] * cx));
+        *reinterpret_cast<uint4*>(stage + lane * 64 + c * 16) =
+            make_uint4(pack2(e[0], e[1]), pack2(e[2], e[3]), pack2(e[4], e[5]), pack2(e[6], e[7]));
+      }
+      ptx::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_3d(&tmap_out, stage, h * kD + gi * 32, tp * kQTile + q * 32, f);
+        ptx::bulk_commit_group();
+      }
+      if (trc) TR(gi * 512 + last * 16 + 9);
+    };
+
+    ptx::mbar_wait(&bars->x_full, 0);
+    if (gi == 1) {
+      // Run the two key groups out of phase: while one is in its exp2 stretch (MUFU bound) the other loads, reduces, merges
+      // or waits.  Nothing below re-aligns them: the groups only meet through mbarriers that are long complete when polled.
+      ptx::mbar_wait(&bars->s_full[1][0], 0);
+      const long long t0 = clock64();
+      while (clock64() - t0 < kStagger) { }
+    }
+    int n = 0;
     for (int t = 0; t < kQTiles; ++t) {
-      const uint32_t to = tmem_base + lane_base + kTmemO + (uint32_t)((t & 1) * kD + hf * 32);
-      m = -INFINITY; l = 0.f;
-      for (int j = 0; j < kBlocks; ++j) {
-        const int g = t * kBlocks + j, b = g & 1, n = g >> 1;
-        const uint32_t ts = tmem_base + lane_base + kTmemS + (uint32_t)(b * kBlk);
-        // number of valid (un-masked) columns among this thread's columns, and where they start
-        const int col0 = j < 3 ? hf * 96 : 0;
-        const int nvalid = j < 3 ? 96 : (hf == 0 ? kS - 3 * kBlk : 0);         // 96 / 1 / 0
-        const bool trc = (warp == 0 && lane == 0 && g < 12);
-        if (trc) TR(g * 16 + 0);
-        ptx::mbar_wait(&bars->s_full[b], (uint32_t)(n & 1));
+      for (int j = 0; j < kNBlk; ++j, ++n) {
+        const int b = n & 1;
+        const uint32_t ts = tmem_s0 + (uint32_t)(b * kBlk);
+        if (trc) TR(gi * 512 + n * 16 + 0);
+        ptx::mbar_wait(&bars->s_full[gi][b], (uint32_t)((n >> 1) & 1));
         ptx::tcgen05_fence_after();
-        if (trc) TR(g * 16 + 1);
+        if (trc) TR(gi * 512 + n * 16 + 1);
         uint32_t v[3][32];
-        if (j < 3) {
-          ptx::tmem_ld_32x32b_x32(ts + (uint32_t)col0, v[0]);
-          ptx::tmem_ld_32x32b_x32(ts + (uint32_t)col0 + 32u, v[1]);
-          ptx::tmem_ld_32x32b_x32(ts + (uint32_t)col0 + 64u, v[2]);
-        } else if (hf == 0) {
-          tmem_ld_32x32b_x16(ts, v[0]);
+        ptx::tmem_ld_32x32b_x32(ts, v[0]);
+        ptx::tmem_ld_32x32b_x32(ts + 32u, v[1]);
+        ptx::tmem_ld_32x32b_x32(ts + 64u, v[2]);
+        float dot = 0.f;
+        if (j == 0) {
+          // this thread's half of q_r . k_576, while the TMEM load is in flight.  The Q tile stays put until both
+          // issuers have committed the tile's last S product, which cannot happen before this thread hands over P of
+          // this very block; the wait below is only the acquire on the TMA-written tile.
+          ptx::mbar_wait(&bars->q_full[t & 1], (uint32_t)((t >> 1) & 1));
+          const uint8_t* qrow = smem + kSmemQ + (t & 1) * kQBytes + r * kRowBytes;
+          const uint4* kx = reinterpret_cast<const uint4*>(smem + kSmemK + kXKey * kRowBytes) + gi * 4;
+          float d4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            float qf[8], kf[8];
+            unpack8(*reinterpret_cast<const uint4*>(qrow + (((gi * 4 + c) ^ (r & 7)) << 4)), qf);
+            unpack8(kx[c], kf);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) d4[i & 3] = fmaf(qf[i], kf[i], d4[i & 3]);
+          }
+          dot = (d4[0] + d4[1]) + (d4[2] + d4[3]);
         }
         ptx::tmem_ld_wait();
-        if (trc) TR(g * 16 + 2);
-        float mx = -INFINITY;
-        if (j < 3) {
-          float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        if (trc) TR(gi * 512 + n * 16 + 2);
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-          for (int c = 0; c < 3; ++c)
+        for (int c = 0; c < 3; ++c)
 #pragma unroll
-            for (int i = 0; i < 32; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(v[c][i]));
-          mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
-        } else if (hf == 0) {
-          mx = __uint_as_float(v[0][0]);                               // key 576, the only valid one of the tail
-        }
-        xmax[(b * 2 + hf) * 128 + r] = mx;
-        // Both warps of this row group have S_j in registers past this barrier, so P_j may overwrite it.
-        named_bar_sync(1 + q, 64);
-        mx = fmaxf(mx, xmax[(b * 2 + (hf ^ 1)) * 128 + r]);
-        const float m_blk = mx * kLog2e;                               // exp2 domain; finite; same in both threads of a row
+          for (int i = 0; i < 32; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(v[c][i]));
+        const float m_blk = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * kLog2e;   // exp2 domain; finite
         if (j == 0) {
-          m = m_blk;                                                   // fresh accumulator, nothing to rescale
+          m = m_blk; l = 0.f;                                          // fresh accumulator, nothing to rescale
         } else {
           // Lazy rescale: only when this block raises the row maximum by more than 2^8 are the accumulator and the
           // running sum moved to the new frame; otherwise the stale maximum stays and p may reach 256.
           const bool need = m_blk - m > 8.0f;
           if (__any_sync(0xffffffffu, need)) {
             const float fac = need ? ex2(m - m_blk) : 1.0f;
-            // P V of block g-1 must have retired (blocks <= g-2 have: S_g was committed after them, so this barrier is
+            // P V of block n-1 must have retired (blocks <= n-2 have: S_n was committed after them, so this barrier is
             // at most one phase behind and the parity wait is exact)
-            ptx::mbar_wait(&bars->o_done[(g - 1) & 1], (uint32_t)(((g - 1) >> 1) & 1));
+            ptx::mbar_wait(&bars->o_done[gi][(n - 1) & 1], (uint32_t)(((n - 1) >> 1) & 1));
             ptx::tcgen05_fence_after();
-            uint32_t a[32];
-            ptx::tmem_ld_32x32b_x32(to, a);
-            ptx::tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) a[i] = __float_as_uint(__uint_as_float(a[i]) * fac);
-            tmem_st_32x32b_x16(to, a);
-            tmem_st_32x32b_x16(to + 16u, a + 16);
+            for (int c = 0; c < 2; ++c) {
+              uint32_t a[32];
+              ptx::tmem_ld_32x32b_x32(tmem_o + (uint32_t)(32 * c), a);
+              ptx::tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) a[i] = __float_as_uint(__uint_as_float(a[i]) * fac);
+              tmem_st_32x32b_x16(tmem_o + (uint32_t)(32 * c), a);
+              tmem_st_32x32b_x16(tmem_o + (uint32_t)(32 * c + 16), a + 16);
+            }
             l *= fac;
             if (need) m = m_blk;
           }
         }
-        const float m_new = m;
-        if (trc) TR(g * 16 + 3);
-        float s4[4] = {0.f, 0.f, 0.f, 0.f};
-        // P_j (bf16 pairs) goes to columns [hf*48, hf*48+48) of the S_j buffer
-        const uint32_t tp = ts + (uint32_t)(hf * 48);
-        if (j < 3) {
+        if (trc) TR(gi * 512 + n * 16 + 3);
+        // exp2 on packed fp32x2 instructions (FFMA2 / FADD2): scale, cubic and row sum cost half the issue slots
+        float2 s2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+        const float2 sc = make_float2(kLog2e, kLog2e), nm = make_float2(-m, -m);
 #pragma unroll
-          for (int c = 0; c < 3; ++c) {
-            uint32_t w[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              const float x0 = fmaf(__uint_as_float(v[c][2 * i]), kLog2e, -m_new);
-              const float x1 = fmaf(__uint_as_float(v[c][2 * i + 1]), kLog2e, -m_new);
-              const float p0 = ex2(x0);
-              const float p1 = (i & 1) ? ex2_poly(x1) : ex2(x1);
-              s4[i & 3] += p0 + p1;
-              w[i] = pack2(p0, p1);
-            }
-            tmem_st_32x32b_x16(tp + (uint32_t)(16 * c), w);
-          }
-        } else if (hf == 0) {
+        for (int c = 0; c < 3; ++c) {
           uint32_t w[16];
-          const float p0 = ex2(fmaf(__uint_as_float(v[0][0]), kLog2e, -m_new));
-          s4[0] = p0;
-          w[0] = pack2(p0, 0.f);
 #pragma unroll
-          for (int i = 1; i < 16; ++i) w[i] = 0u;
-          tmem_st_32x32b_x16(ts, w);                                   // 16 tail keys -> 8 columns used by the MMA
+          for (int i = 0; i < 16; ++i) {
+            const float2 x = ffma2(make_float2(__uint_as_float(v[c][2 * i]), __uint_as_float(v[c][2 * i + 1])), sc, nm);
+            float2 p;
+            if (kPolyEvery > 0 && (i % (kPolyEvery > 0 ? kPolyEvery : 1)) == kPolyEvery - 1) {
+              p = ex2_poly2(x);
+            } else {
+              p.x = ex2(x.x); p.y = ex2(x.y);
+            }
+            s2[i & 1] = fadd2(s2[i & 1], p);
+            w[i] = pack2(p.x, p.y);
+          }
+          tmem_st_32x32b_x16(ts + (uint32_t)(16 * c), w);             // P over S: column c <- keys 2c, 2c+1
         }
-        const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
-        (void)nvalid; (void)col0;
-        if (trc) TR(g * 16 + 4);
+        l += (s2[0].x + s2[0].y) + (s2[1].x + s2[1].y);
+        if (trc) TR(gi * 512 + n * 16 + 4);
         tmem_st_wait();
         ptx::tcgen05_fence_before();
-        ptx::mbar_arrive(&bars->p_full[b]);
-        if (trc) TR(g * 16 + 5);
-        l += sum;
-        if (trc) TR(g * 16 + 7);
-      }
-      // end of the tile: once the last P V has retired read the accumulator, combine the two halves' row sums,
-      // normalise and store
-      {
-        const int g = t * kBlocks + kBlocks - 1;
-        xsum[hf * 128 + r] = l;
-        ptx::mbar_wait(&bars->o_done[g & 1], (uint32_t)((g >> 1) & 1));
-        ptx::tcgen05_fence_after();
-        uint32_t vo[32];
-        ptx::tmem_ld_32x32b_x32(to, vo);
-        ptx::tmem_ld_wait();
-        ptx::tcgen05_fence_before();
-        ptx::mbar_arrive(&bars->o_free[t & 1]);
-        named_bar_sync(1 + q, 64);
-        const float inv = 1.0f / (l + xsum[(hf ^ 1) * 128 + r]);
-        const int row = t * kQTile + r;
-        if (row < kS) {
-          uint4* dst = reinterpret_cast<uint4*>(out + ((size_t)f * kS + row) * (kHeads * kD) + h * kD + hf * 32);
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            float e[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) e[i] = __uint_as_float(vo[8 * c + i]) * inv;
-            dst[c] = make_uint4(pack2(e[0], e[1]), pack2(e[2], e[3]), pack2(e[4], e[5]), pack2(e[6], e[7]));
-          }
+        ptx::mbar_arrive(&bars->p_full[gi][b]);
+        if (trc) TR(gi * 512 + n * 16 + 5);
+        if (j == 0) {
+          // With this tile's first block handed to the tensor pipe, finish the previous tile: its last P V has had a whole
+          // block's time to retire, so the waits inside return at once.
+          if (t > 0) merge(t - 1);
+          dot_cur = dot;
+        } else if (j == kNBlk - 1) {
+          publish(t);
         }
-        named_bar_sync(1 + q, 64);                                     // xsum is rewritten by the next tile
       }
     }
+    merge(kQTiles - 1);
+    if (lane == 0) ptx::bulk_wait_group_read<0>();
   }
 
   ptx::tcgen05_fence_before();
@@ -407,23 +494,18 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 static EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
+  static EncodeTiledFn fn = [] {
     void* p = nullptr;
     cudaDriverEntryPointQueryResult qres;
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
         qres == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  });
+      return reinterpret_cast<EncodeTiledFn>(p);
+    return (EncodeTiledFn) nullptr;
+  }();
   return fn;
 }
 }  // namespace at5
 
-int attention_impl(const void* qkv, int n_frames_total, void* out, cudaStream_t stream, long long* trace);
-int attention(const void* qkv, int n_frames_total, void* out, cudaStream_t stream) {
-  return attention_impl(qkv, n_frames_total, out, stream, nullptr);
-}
 int attention_impl(const void* qkv, int n_frames_total, void* out, cudaStream_t stream, long long* trace) {
   using namespace at5;
   EGPT_CHECK_ARG(qkv && out && n_frames_total > 0, "attention: bad arguments");
@@ -431,35 +513,48 @@ int attention_impl(const void* qkv, int n_frames_total, void* out, cudaStream_t 
   EncodeTiledFn fn = encode_fn();
   if (!fn) { set_error("cuTensorMapEncodeTiled entry point not available"); return EGPT_ERR_CUDA; }
   // qkv viewed as [F][577][3072]; rows past 577 of a frame are out of bounds -> zero filled
-  CUtensorMap tm;
+  CUtensorMap tm_q, tm_kv;
   cuuint64_t dims[3] = {3 * kHeads * kD, (cuuint64_t)kS, (cuuint64_t)n_frames_total};
   cuuint64_t strides[2] = {(cuuint64_t)3 * kHeads * kD * 2, (cuuint64_t)kS * 3 * kHeads * kD * 2};
-  cuuint32_t box[3] = {kD, 64, 1};
   cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = fn(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(qkv), dims, strides, box, estr,
+  cuuint32_t box_q[3] = {kD, 64, 1}, box_kv[3] = {kD, 16, 1};
+  CUresult r = fn(&tm_q, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(qkv), dims, strides, box_q, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r == CUDA_SUCCESS)
+    r = fn(&tm_kv, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(qkv), dims, strides, box_kv, estr,
+           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  // out viewed as [F][577][1024]: a warp stores 32 rows x 32 dims at a time, rows past 577 are clipped
+  CUtensorMap tm_out;
+  cuuint64_t odims[3] = {kHeads * kD, (cuuint64_t)kS, (cuuint64_t)n_frames_total};
+  cuuint64_t ostrides[2] = {(cuuint64_t)kHeads * kD * 2, (cuuint64_t)kS * kHeads * kD * 2};
+  cuuint32_t box_o[3] = {32, 32, 1};
+  if (r == CUDA_SUCCESS)
+    r = fn(&tm_out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, out, odims, ostrides, box_o, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_error("attention: cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return EGPT_ERR_CUDA; }
-  CUtensorMap tm_tail;
-  cuuint32_t box_tail[3] = {kD, kTail, 1};
-  r = fn(&tm_tail, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(qkv), dims, strides, box_tail, estr,
-         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) { set_error("attention: cuTensorMapEncodeTiled (tail) failed with CUresult %d", (int)r); return EGPT_ERR_CUDA; }
   // per launch: the attribute is per device, and one process may drive several GPUs
   EGPT_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
   ProfScope prof(PROF_ATTN, 4.0 * kS * kS * kD * kHeads * (double)n_frames_total, stream);
-  attention_tc_kernel<<<n_frames_total * kHeads, kThreads, kSmemTotal, stream>>>(tm, tm_tail, reinterpret_cast<__nv_bfloat16*>(out), trace);
+  attention_tc_kernel<<<n_frames_total * kHeads, kThreads, kSmemTotal, stream>>>(tm_q, tm_kv, tm_out, trace);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
 }
 
+int attention(const void* qkv, int n_frames_total, void* out, cudaStream_t stream) {
+  return attention_impl(qkv, n_frames_total, out, stream, nullptr);
+}
+
 }  // namespace egpt
 
-// developer aid: clock64 timestamps of CTA 0's phases (softmax warp 4 lane 0: slots g*16+k; MMA thread: 256+g*8+k)
+#ifdef EGPT_ATTN_TRACE
+// developer aid (tools/attn_trace.py): clock64 stamps of CTA 0 -- softmax warps 0 / 4 lane 0 at trace[group*512 + n*16 + k],
+// the two MMA issuers at trace[1024 + group*256 + n*8 + k]
 extern "C" int egpt_attention_trace(const uint16_t* qkv, int n_frames_total, uint16_t* out, long long* trace, void* stream) {
   return egpt::attention_impl(qkv, n_frames_total, out, (cudaStream_t)stream, trace);
 }
+#endif
 
 extern "C" int egpt_attention(const uint16_t* qkv, int n_frames_total, uint16_t* out, void* stream) {
   return egpt::attention(qkv, n_frames_total, out, (cudaStream_t)stream);
