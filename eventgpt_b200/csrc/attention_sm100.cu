@@ -48,10 +48,16 @@ constexpr int kSmemXch = kSmemBar + 512;                  // float [3 (max, sum,
 constexpr int kSmemStage = kSmemXch + 6 * 1024;           // output staging: 8 warps x (32 rows x 64 B)
 constexpr int kStageBytes = 32 * 64;
 constexpr int kSmemTotal = kSmemStage + 8 * kStageBytes + 1024;   // + alignment slack
-constexpr int kStagger = 900;                             // cycles by which key group 1 starts behind group 0
+#ifndef EGPT_ATTN_STAGGER
+#define EGPT_ATTN_STAGGER 900
+#endif
+constexpr int kStagger = EGPT_ATTN_STAGGER;                             // cycles by which key group 1 starts behind group 0
 constexpr int kTmemCols = 512;
 constexpr uint32_t kTmemS = 0, kTmemO = 4 * kBlk;         // columns: S/P [group][buffer][96], then O [group][64]
-constexpr int kPolyEvery = 4;                             // every kPolyEvery-th pair of exp2 runs as a cubic on the FMA pipe (0: none)
+#ifndef EGPT_ATTN_POLY_EVERY
+#define EGPT_ATTN_POLY_EVERY 4
+#endif
+constexpr int kPolyEvery = EGPT_ATTN_POLY_EVERY;                             // every kPolyEvery-th pair of exp2 runs as a cubic on the FMA pipe (0: none)
 
 // MN-major B operand (V block: rows = keys (K), 64 contiguous dims (N) = 128 B per key, SWIZZLE_128B):
 // 8-key groups are 1024 B apart (SBO); a single 64-wide N block, so LBO is unused.
@@ -186,7 +192,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
 #endif
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   Bars* bars = reinterpret_cast<Bars*>(smem + kSmemBar);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);    // warp-uniform by construction
+  const int lane = threadIdx.x & 31;
   const int f = blockIdx.x / kHeads, h = blockIdx.x % kHeads;
 
   if (warp == 8 && lane == 0) { ptx::prefetch_tensormap(&tmap_q); ptx::prefetch_tensormap(&tmap_kv); ptx::prefetch_tensormap(&tmap_out); }
@@ -210,7 +217,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   ptx::tcgen05_fence_before();
   __syncthreads();
   ptx::tcgen05_fence_after();
-  const uint32_t tmem_base = bars->tmem_ptr;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, bars->tmem_ptr, 0);
 
   if (warp >= 8) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
@@ -246,8 +253,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         ptx::mbar_wait(&bars->q_empty[t & 1], (uint32_t)(((t >> 1) - 1) & 1));   // both groups' last Q K^T of tile t-2 retired
         load_q(t);
       }
-    } else if ((warp == 9 || warp == 11) && lane == 0) {
-      // ===== MMA issuer of key group gi: an independent in-order stream of S and P V products =====
+    } else if (warp == 9 || warp == 11) {
+      // ===== MMA issuer of key group gi: an independent in-order stream of S and P V products.  The whole warp walks the
+      // loop (uniform control flow and operands); one elected lane issues =====
       const int gi = warp == 9 ? 0 : 1;
       const uint64_t dK0 = ptx::make_smem_desc_sw128(ptx::smem_u32(smem + kSmemK + gi * kGroupKeys * kRowBytes));
       const uint64_t dV0 = make_desc_mn_sw128(ptx::smem_u32(smem + kSmemV + gi * kGroupKeys * kRowBytes));
@@ -268,10 +276,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         const uint32_t tmem_p = tmem_s0 + (uint32_t)(b * kBlk);
         // A = P from TMEM: 16 keys = 8 packed columns per k-step; B = V rows 16*kk .. +15 of the block (2048 B = 128 units)
         const uint64_t dv = dV0 + (uint64_t)(j * (kBlk * kRowBytes >> 4));
+        if (ptx::elect_one()) {
 #pragma unroll
-        for (int kk = 0; kk < kBlk / 16; ++kk)
-          umma_bf16_ts(tmem_o, tmem_p + (uint32_t)(kk * 8), dv + (uint64_t)(kk * 128), idesc_pv, (j != 0 || kk != 0) ? 1u : 0u);
-        ptx::umma_commit(&bars->o_done[gi][b]);
+          for (int kk = 0; kk < kBlk / 16; ++kk)
+            umma_bf16_ts(tmem_o, tmem_p + (uint32_t)(kk * 8), dv + (uint64_t)(kk * 128), idesc_pv, (j != 0 || kk != 0) ? 1u : 0u);
+          ptx::umma_commit(&bars->o_done[gi][b]);
+        }
+        __syncwarp();
         TR(1024 + gi * 256 + n * 8 + 4);
       };
       int n = 0;
@@ -286,11 +297,14 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           ptx::tcgen05_fence_after();
           const uint32_t tmem_s = tmem_s0 + (uint32_t)((n & 1) * kBlk);
           const uint64_t dk = dK0 + (uint64_t)(j * (kBlk * kRowBytes >> 4));
+          if (ptx::elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kD / 16; ++k) ptx::umma_bf16_ss(tmem_s, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc_s, k != 0);
-          ptx::umma_commit(&bars->s_full[gi][n & 1]);
+            for (int k = 0; k < kD / 16; ++k) ptx::umma_bf16_ss(tmem_s, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc_s, k != 0);
+            ptx::umma_commit(&bars->s_full[gi][n & 1]);
+            if (j == kNBlk - 1) ptx::umma_commit(&bars->q_empty[t & 1]);
+          }
+          __syncwarp();
           TR(1024 + gi * 256 + n * 8 + 1);
-          if (j == kNBlk - 1) ptx::umma_commit(&bars->q_empty[t & 1]);
           if (n >= 1) issue_pv(n - 1);
         }
       }
