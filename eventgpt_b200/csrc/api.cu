@@ -145,11 +145,18 @@ static int run_projector(egpt_handle* hd, int F, TowerWs& w, uint16_t* dst, cuda
   return EGPT_OK;
 }
 
-// ws.z [B,n,577,4096] -> pooled [B,n+577,4096] -> feature_adaptor -> out_tokens
-static int run_pool_adaptor(egpt_handle* hd, int B, int n, TowerWs& w, uint16_t* out_tokens, cudaStream_t st) {
-  EGPT_TRY(egpt_spatio_temporal_pool(w.z, 0, B, n, kTok, kLlm, n, w.pooled, w.pool_partial, w.pool_partial_bytes, st));
-  EGPT_TRY(gemm_bf16(w.pooled, hd->adaptor_w, hd->adaptor_b, out_tokens, (long long)B * (n + kTok), kLlm, kLlm,
-                     EPI_BIAS_BF16, st));
+// ws.h (fp32 last_hidden_state of B windows x n frames) -> out_tokens [B, n+577, 4096]:
+//   feature_adaptor(get_spatio_temporal_features(visual_projector(h)))          (model/EventChatModel.py:194-200, 326-343)
+// The projector is Linear -> GELU -> Linear and the pooling is a mean, so the second Linear (affine) commutes with it:
+//   pool(W2 g + b2) = W2 pool(g) + b2.  Pooling the GELU output first shrinks the second projector GEMM from
+// n*577 to n+577 rows per window (5x fewer at n = 5); the adaptor then runs on the same pooled rows.
+static int run_projector_pool_adaptor(egpt_handle* hd, int B, int n, TowerWs& w, uint16_t* out_tokens, cudaStream_t st) {
+  const long long M = (long long)B * n * kTok, Mo = (long long)B * (n + kTok);
+  EGPT_TRY(f32_to_bf16(w.h, w.y, M * kHid, st));
+  EGPT_TRY(gemm_bf16(w.y, hd->proj0_w, hd->proj0_b, w.mlp, M, kLlm, kHid, EPI_GELU_BF16, st));
+  EGPT_TRY(egpt_spatio_temporal_pool(w.mlp, 0, B, n, kTok, kLlm, n, w.pooled, w.pool_partial, w.pool_partial_bytes, st));
+  EGPT_TRY(gemm_bf16(w.pooled, hd->proj2_w, hd->proj2_b, w.z, Mo, kLlm, kLlm, EPI_BIAS_BF16, st));
+  EGPT_TRY(gemm_bf16(w.z, hd->adaptor_w, hd->adaptor_b, out_tokens, Mo, kLlm, kLlm, EPI_BIAS_BF16, st));
   return EGPT_OK;
 }
 
@@ -327,8 +334,7 @@ extern "C" int egpt_encode_pool(egpt_handle* h, const uint16_t* pixel_values, in
   EGPT_WS_OR_FAIL(F);
   EGPT_TRY(im2col(pixel_values, w.qkv, F, st));
   EGPT_TRY(run_tower_from_patches(h, F, w, st));
-  EGPT_TRY(run_projector(h, F, w, w.z, st));
-  EGPT_TRY(run_pool_adaptor(h, n_windows, n_frames, w, out_tokens, st));
+  EGPT_TRY(run_projector_pool_adaptor(h, n_windows, n_frames, w, out_tokens, st));
   return EGPT_OK;
 }
 
@@ -373,7 +379,6 @@ extern "C" int egpt_visual_tokens(egpt_handle* h, const void* x, const void* y, 
   // resized + normalised pixels go straight into the im2col layout of the patch GEMM
   EGPT_TRY(egpt_preprocess(frames, frame_stride, out_hw, F, H, nullptr, w.qkv, status, pre_ws, pws, st));
   EGPT_TRY(run_tower_from_patches(h, F, w, st));
-  EGPT_TRY(run_projector(h, F, w, w.z, st));
-  EGPT_TRY(run_pool_adaptor(h, n_windows, n_frames, w, out_tokens, st));
+  EGPT_TRY(run_projector_pool_adaptor(h, n_windows, n_frames, w, out_tokens, st));
   return EGPT_OK;
 }
