@@ -66,3 +66,59 @@ def window_offsets_from_ms_index(ms_to_idx, window_ms=50, first_ms=0, n_windows=
     avail = (len(ms2idx) - 1 - first_ms) // window_ms
     n = avail if n_windows is None else min(int(n_windows), avail)
     return ms2idx[first_ms + window_ms * np.arange(n + 1)]
+
+
+def split_event_by_time_clips(event_npy, time_interval=50000, image_timestamps=None):
+    """Mirror of ``split_event_by_time`` of the DSEC clip builder
+    (feasible/my_egpt_dsec_dataset/build_my_egpt_dsec_seq.py:137-225): 50 %-overlapping clips anchored at the image
+    timestamps, empty clips dropped, same metadata; fixed bins when there are no timestamps or no clip holds an event.
+    Instead of one boolean mask over the whole recording per clip, the clip bounds come from two binary searches over the
+    (sorted, or argsorted once) timestamps; each clip additionally carries ``start`` / ``end``, the slice of the
+    time-ordered stream it covers, which is what ``clips_to_batch`` consumes."""
+    t = np.asarray(event_npy["t"])
+    if image_timestamps is not None and len(image_timestamps) > 0:
+        ts = np.asarray(image_timestamps, dtype=np.int64)
+        seq_start, seq_end = int(ts.min()), int(ts.max())
+        step = time_interval // 2
+        n_clips = max(0, (seq_end - time_interval - seq_start) // step + 1) if seq_end - seq_start >= time_interval else 0
+        starts_us = seq_start + step * np.arange(n_clips, dtype=np.int64)
+        is_sorted = bool(np.all(t[1:] >= t[:-1])) if len(t) > 1 else True
+        order = None if is_sorted else np.argsort(t, kind="stable")
+        ts_sorted = t if is_sorted else t[order]
+        lo = np.searchsorted(ts_sorted, starts_us, side="left")
+        hi = np.searchsorted(ts_sorted, starts_us + time_interval, side="left")
+        ts_order = np.argsort(ts, kind="stable")
+        ts_asc = ts[ts_order]
+        out = []
+        for c in range(n_clips):
+            s, e = int(lo[c]), int(hi[c])
+            if e <= s:
+                continue
+            cs, ce = int(starts_us[c]), int(starts_us[c]) + time_interval
+            a, b = np.searchsorted(ts_asc, cs, side="left"), np.searchsorted(ts_asc, ce, side="left")
+            imgs = sorted(int(i) for i in ts_order[a:b])
+            idx = np.arange(s, e) if is_sorted else np.sort(order[s:e])
+            out.append({"indices": idx, "start": s, "end": e, "time_start": cs, "time_end": ce,
+                        "duration_ms": time_interval / 1000000.0 * 1000.0, "image_timestamp": ce,
+                        "image_idx": imgs[0] if imgs else c, "image_indices_in_clip": imgs, "num_events": e - s})
+        if out:
+            return out
+    p, x, y = np.asarray(event_npy["p"]), np.asarray(event_npy["x"]), np.asarray(event_npy["y"])
+    bins = (t // time_interval) * time_interval
+    out = []
+    for b in np.unique(bins):
+        m = bins == b
+        out.append({"p": p[m], "t": t[m], "x": x[m], "y": y[m], "time_start": b, "time_end": b + time_interval,
+                    "duration_ms": time_interval / 1000.0})
+    return out
+
+
+def clips_to_batch(event_npy, clips):
+    """Overlapping clips -> one ragged batch for ``events.raster`` / ``visual_tokens``: the clips' events back to back
+    (an event in the overlap of two clips appears in both) and the CSR offsets [len(clips) + 1]."""
+    x, y, p = (np.asarray(event_npy[k]) for k in "xyp")
+    idx = [c["indices"] for c in clips]
+    offsets = np.zeros(len(clips) + 1, dtype=np.int64)
+    np.cumsum([len(i) for i in idx], out=offsets[1:])
+    cat = np.concatenate(idx) if idx else np.zeros(0, dtype=np.int64)
+    return x[cat], y[cat], p[cat], offsets

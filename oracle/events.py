@@ -96,3 +96,37 @@ def split_event_by_time(event_npy, time_interval=50000):
         m = bins == b
         out.append({'p': p[m], 't': t[m], 'x': x[m], 'y': y[m]})
     return out
+
+
+def split_event_by_time_clips(event_npy, time_interval=50000, image_timestamps=None):
+    """feasible/my_egpt_dsec_dataset/build_my_egpt_dsec_seq.py:137-225: with image timestamps, sequential clips
+    of ``time_interval`` us stepping by half a clip from the first image timestamp while the clip ends no later
+    than the last one; a clip with no event is dropped; each clip carries the ascending event indices
+    (``np.where(mask)``) and its metadata.  Without timestamps (or when no clip holds an event): fixed bins as in
+    common/common.py, each with start / end / duration."""
+    p, t, x, y = event_npy['p'], event_npy['t'], event_npy['x'], event_npy['y']
+    if image_timestamps is not None and len(image_timestamps) > 0:
+        out = []
+        seq_start, seq_end = min(image_timestamps), max(image_timestamps)
+        step = time_interval // 2
+        clip_start, clip_idx = seq_start, 0
+        while clip_start + time_interval <= seq_end:
+            clip_end = clip_start + time_interval
+            idx = np.where((t >= clip_start) & (t < clip_end))[0]
+            if len(idx) > 0:
+                imgs = [i for i, ts in enumerate(image_timestamps) if clip_start <= ts < clip_end]
+                out.append({'indices': idx, 'time_start': clip_start, 'time_end': clip_end,
+                            'duration_ms': time_interval / 1000000.0 * 1000.0, 'image_timestamp': clip_end,
+                            'image_idx': imgs[0] if imgs else clip_idx, 'image_indices_in_clip': imgs,
+                            'num_events': len(idx)})
+            clip_start += step
+            clip_idx += 1
+        if out:
+            return out
+    bins = (t // time_interval) * time_interval
+    out = []
+    for b in np.unique(bins):
+        m = bins == b
+        out.append({'p': p[m], 't': t[m], 'x': x[m], 'y': y[m], 'time_start': b, 'time_end': b + time_interval,
+                    'duration_ms': time_interval / 1000.0})
+    return out

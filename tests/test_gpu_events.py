@@ -234,3 +234,31 @@ def test_split_dsec_window_and_large_sorted_stream(dev):
     for g, w in zip(got, want):
         for k in "xytp":
             assert np.array_equal(g[k], w[k])
+
+
+def test_overlap_clips_rasterise_like_reference(dev):
+    """50 %-overlap clips of a recording (build_my_egpt_dsec_seq.py:137-202) as one ragged raster batch: every clip's five
+    frames equal the reference rasterisation of that clip's events (events in an overlap are rasterised in both clips)."""
+    from eventgpt_b200 import events as E, io as eio
+    from oracle import events as oev
+    rng = np.random.default_rng(21)
+    n, H, W = 120_000, 120, 160
+    t = np.sort(rng.integers(2_000_000, 2_400_000, n)).astype(np.int64)
+    t = t[(t < 2_150_000) | (t >= 2_230_000)]            # an 80 ms hole: one clip vanishes, its neighbours are ragged
+    n = len(t)
+    ev = dict(x=rng.integers(0, W, n).astype(np.uint16), y=rng.integers(0, H, n).astype(np.uint16),
+              p=rng.integers(0, 2, n).astype(np.uint8), t=t)
+    stamps = [2_000_000 + 50_000 * i for i in range(9)]
+    clips = eio.split_event_by_time_clips(ev, 50_000, stamps)
+    want_clips = oev.split_event_by_time_clips(ev, 50_000, stamps)
+    assert len(clips) == len(want_clips) and 10 <= len(clips) < 15
+    x, y, p, off = eio.clips_to_batch(ev, clips)
+    dx, dy, dp = _dev_events(dict(x=x, y=y, p=p), dev)
+    fr, hw, _, st = E.raster(dx, dy, dp, torch.tensor(off, dtype=torch.int64, device=dev), len(clips), 5, H, W)
+    E.check_status(st, "clips")
+    got = E.frames_to_numpy(fr, hw)
+    for b, c in enumerate(want_clips):
+        sub = {k: ev[k][c["indices"]] for k in "xypt"}
+        want = oev.get_event_images_list(sub, 5)
+        for i in range(5):
+            assert np.array_equal(got[b * 5 + i], want[i]), (b, i)

@@ -52,3 +52,54 @@ def test_window_offsets_feed_the_rasteriser_layout():
         assert w.size == 0 or (w.min() >= i * 50_000 and w.max() < (i + 1) * 50_000)
         sl = eio.extract_from_h5_by_index(f, offs[i], offs[i + 1])
         assert len(sl["t"]) == offs[i + 1] - offs[i] and eio.get_num_events(f) == 200_000
+
+
+# ---- 50 %-overlap clip splitter (build_my_egpt_dsec_seq.py:137-225) ---------------------------------------------
+
+def _clip_recording(seed, n=50_000, dur_us=600_000, sort=True, gap=None):
+    rng = np.random.default_rng(seed)
+    t = rng.integers(1_000_000, 1_000_000 + dur_us, n).astype(np.int64)
+    if gap is not None:                                  # a stretch without events -> dropped clips
+        t = t[(t < gap[0]) | (t >= gap[1])]
+    if sort:
+        t = np.sort(t)
+    n = len(t)
+    return {"x": rng.integers(0, 640, n).astype(np.uint16), "y": rng.integers(0, 480, n).astype(np.uint16),
+            "p": rng.integers(0, 2, n).astype(np.uint8), "t": t}
+
+
+@pytest.mark.parametrize("sort", [True, False])
+@pytest.mark.parametrize("interval", [50_000, 33_333])
+def test_overlap_clips_match_oracle(sort, interval):
+    from oracle import events as OE
+    ev = _clip_recording(3, sort=sort, gap=(1_200_000, 1_290_000))
+    stamps = [1_000_000 + 50_000 * i for i in range(12)]
+    stamps[3], stamps[7] = stamps[7], stamps[3]          # the reference only takes min / max and scans the list
+    want = OE.split_event_by_time_clips(ev, interval, stamps)
+    got = eio.split_event_by_time_clips(ev, interval, stamps)
+    assert len(got) == len(want) and len(got) > 5
+    assert any(w["num_events"] != want[0]["num_events"] for w in want)
+    for g, w in zip(got, want):
+        np.testing.assert_array_equal(g["indices"], w["indices"])
+        for k in ("time_start", "time_end", "duration_ms", "image_timestamp", "image_idx", "image_indices_in_clip", "num_events"):
+            assert g[k] == w[k], k
+    # consecutive clips overlap by half a clip
+    assert got[1]["time_start"] - got[0]["time_start"] == interval // 2
+    x, y, p, off = eio.clips_to_batch(ev, got)
+    assert off[-1] == sum(w["num_events"] for w in want) and len(x) == off[-1]
+    for i, w in enumerate(want):
+        np.testing.assert_array_equal(x[off[i]:off[i + 1]], ev["x"][w["indices"]])
+        np.testing.assert_array_equal(p[off[i]:off[i + 1]], ev["p"][w["indices"]])
+
+
+def test_overlap_clips_fallbacks():
+    from oracle import events as OE
+    ev = _clip_recording(4, n=5_000)
+    for stamps in (None, [], [1_000_000, 1_020_000], [5_000_000, 5_200_000]):   # none / too short a span / no events inside
+        want = OE.split_event_by_time_clips(ev, 50_000, stamps)
+        got = eio.split_event_by_time_clips(ev, 50_000, stamps)
+        assert len(got) == len(want) and "indices" not in got[0]
+        for g, w in zip(got, want):
+            assert g["time_start"] == w["time_start"] and g["time_end"] == w["time_end"] and g["duration_ms"] == w["duration_ms"]
+            for k in "xytp":
+                np.testing.assert_array_equal(g[k], w[k])
