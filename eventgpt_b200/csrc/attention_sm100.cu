@@ -167,7 +167,8 @@ struct Bars {
   uint64_t p_full[2][2];                 // [group][buffer]: P stored over it by the group's 128 threads
   uint64_t o_done[2][2];                 // [group][block parity]: P V of a block retired
   uint64_t o_free;                       // the tile's two partial outputs were read out by all 256 threads
-  uint64_t x_ready[2];                   // [group]: the group's (max, sum, dot) of a finished tile are in shared memory
+  uint64_t t_done;                       // per tile: both groups' (max, sum, dot) are in shared memory (256 arrivals) and
+                                         // both groups' last P V has retired (2 commits)
   uint32_t tmem_ptr;
 };
 
@@ -201,13 +202,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     for (int g = 0; g < 2; ++g) {
       for (int i = 0; i < kNBlk; ++i) { ptx::mbar_init(&bars->k_full[g][i], 1); ptx::mbar_init(&bars->v_full[g][i], 1); }
       ptx::mbar_init(&bars->q_full[g], 1); ptx::mbar_init(&bars->q_empty[g], 2);
-      ptx::mbar_init(&bars->x_ready[g], 128);
       for (int i = 0; i < 2; ++i) {
         ptx::mbar_init(&bars->s_full[g][i], 1); ptx::mbar_init(&bars->p_full[g][i], 128); ptx::mbar_init(&bars->o_done[g][i], 1);
       }
     }
     ptx::mbar_init(&bars->x_full, 1);
     ptx::mbar_init(&bars->o_free, 256);
+    ptx::mbar_init(&bars->t_done, 258);
     ptx::fence_barrier_init();
   }
   if (warp == 10) {
@@ -281,6 +282,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           for (int kk = 0; kk < kBlk / 16; ++kk)
             umma_bf16_ts(tmem_o, tmem_p + (uint32_t)(kk * 8), dv + (uint64_t)(kk * 128), idesc_pv, (j != 0 || kk != 0) ? 1u : 0u);
           ptx::umma_commit(&bars->o_done[gi][b]);
+          if (j == kNBlk - 1) ptx::umma_commit(&bars->t_done);
         }
         __syncwarp();
         TR(1024 + gi * 256 + n * 8 + 4);
@@ -333,20 +335,19 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       x_t[gi * 128 + r] = m;
       x_t[512 + gi * 128 + r] = l;
       x_t[1024 + gi * 128 + r] = dot_cur;
-      ptx::mbar_arrive(&bars->x_ready[gi]);
+      ptx::mbar_arrive(&bars->t_done);
     };
     auto merge = [&](int tp) {
-      const int last = tp * kNBlk + kNBlk - 1;
+      [[maybe_unused]] const int last = tp * kNBlk + kNBlk - 1;      // trace slot
       const float* x_t = xch + (tp & 1) * 256;
       const float m_me = x_t[gi * 128 + r], l_me = x_t[512 + gi * 128 + r];
-      // The partner group runs on its own clock.  Its numbers for tile tp and its last P V of that tile: both barriers are
-      // at most one phase behind here (the partner cannot finish tile tp+1 before this thread has released o_free).
-      ptx::mbar_wait(&bars->x_ready[gi ^ 1], (uint32_t)(tp & 1));
+      // The partner group runs on its own clock.  One barrier covers everything this merge needs from it and from the
+      // tensor pipe; it cannot run a phase ahead because the next tile's P V products wait for o_free, released below.
+      if (trc) TR(gi * 512 + last * 16 + 10);
+      ptx::mbar_wait(&bars->t_done, (uint32_t)(tp & 1));
+      if (trc) TR(gi * 512 + last * 16 + 7);
       const float mo = x_t[(gi ^ 1) * 128 + r], lo = x_t[512 + (gi ^ 1) * 128 + r];
       const float sx = (x_t[1024 + gi * 128 + r] + x_t[1024 + (gi ^ 1) * 128 + r]) * kLog2e;
-      ptx::mbar_wait(&bars->o_done[gi][last & 1], (uint32_t)((last >> 1) & 1));
-      ptx::mbar_wait(&bars->o_done[gi ^ 1][last & 1], (uint32_t)((last >> 1) & 1));
-      if (trc) TR(gi * 512 + last * 16 + 7);
       ptx::tcgen05_fence_after();
       uint32_t oa[32], ob[32];
       ptx::tmem_ld_32x32b_x32(tmem_o + (uint32_t)(gi * 32), oa);
@@ -364,16 +365,22 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       if (lane == 0) ptx::bulk_wait_group_read<0>();                   // the previous tile's store has read the slab
       __syncwarp();
       const uint4* vx = reinterpret_cast<const uint4*>(smem + kSmemV + kXKey * kRowBytes) + gi * 4;   // row 576: unswizzled
+      const float2 ca2 = make_float2(ca, ca), cb2 = make_float2(cb, cb), cx2 = make_float2(cx, cx), z2 = make_float2(0.f, 0.f);
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
-        float e[8], vf[8];
+        float vf[8];
         unpack8(vx[c], vf);
+        uint32_t w[4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
-          e[i] = fmaf(__uint_as_float(oa[8 * c + i]), ca, fmaf(__uint_as_float(ob[8 * c + i]), cb, vf[i] * cx));
-        *reinterpret_cast<uint4*>(stage + lane * 64 + c * 16) =
-            make_uint4(pack2(e[0], e[1]), pack2(e[2], e[3]), pack2(e[4], e[5]), pack2(e[6], e[7]));
+        for (int i = 0; i < 4; ++i) {
+          float2 e = ffma2(make_float2(vf[2 * i], vf[2 * i + 1]), cx2, z2);
+          e = ffma2(make_float2(__uint_as_float(ob[8 * c + 2 * i]), __uint_as_float(ob[8 * c + 2 * i + 1])), cb2, e);
+          e = ffma2(make_float2(__uint_as_float(oa[8 * c + 2 * i]), __uint_as_float(oa[8 * c + 2 * i + 1])), ca2, e);
+          w[i] = pack2(e.x, e.y);
+        }
+        *reinterpret_cast<uint4*>(stage + lane * 64 + c * 16) = make_uint4(w[0], w[1], w[2], w[3]);
       }
+      if (trc) TR(gi * 512 + last * 16 + 13);
       ptx::fence_proxy_async();
       __syncwarp();
       if (lane == 0) {

@@ -22,10 +22,10 @@ def deltas(row):
 names = ["s_full wait", "ld", "max/rescale", "exps+st issue", "st_wait+arrive"]
 for X in range(2):
     nb = 15
-    print(f"softmax group {X} (warp {4 * X} lane 0): block start, deltas {names}, then merge [o_done, named bar, O loads, stored]")
+    print(f"softmax group {X} (warp {4 * X} lane 0): block start, deltas {names}, then merge [start, tile done, O loaded + o_free, computed + staged, TMA issued]")
     for n in range(nb):
-        row = [rel(x) for x in t[X * 512 + n * 16: X * 512 + n * 16 + 10]]
-        print(f"  n={n:2d} start {row[0]}  {deltas(row[:6])}  end {row[5]}  tile-end {[r for r in row[6:]]}")
+        row = [rel(x) for x in t[X * 512 + n * 16: X * 512 + n * 16 + 14]]
+        print(f"  n={n:2d} start {row[0]}  {deltas(row[:6])}  end {row[5]}  merge {[row[k] for k in (10, 7, 8, 13, 9)] if row[7] else ''}")
 for X in range(2):
     nb = 15
     print(f"issuer {X}: [S issue start, S committed] [pv: p_full wait start, got, committed]")
