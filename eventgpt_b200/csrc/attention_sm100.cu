@@ -3,9 +3,10 @@
 // called from model/EventChatModel.py:196).  Input: packed QKV projection [F*577, 3072] bf16
 // (q pre-scaled by 1/8 in the weights); output bf16 [F*577, 1024].
 //
-// One CTA per (frame, head), 384 threads.  The 577 keys are split into two key groups of 288 (three blocks of
-// 96) plus one left-over key; each group is an independent flash-attention pipeline over the same 128-row Q
-// tile, and the two partial results of a row are merged once per tile:
+// Persistent CTAs of 384 threads, one per SM, each working through a contiguous range of (frame, head, Q tile)
+// units.  The 577 keys of a head are split into two key groups of 288 (three blocks of 96) plus one left-over
+// key; each group is an independent flash-attention pipeline over the same 128-row Q tile, and the two partial
+// results of a row are merged once per tile:
 //   warps 0-3 / 4-7  softmax of key group 0 / 1: one thread per (row, group).  S_n is read from TMEM into
 //              registers, P_n = exp2(S_n - m) goes back over it as packed bf16 (tcgen05.st), the group's partial
 //              output accumulates in TMEM across the three blocks and is rescaled in place only when a block
@@ -14,8 +15,9 @@
 //              (two partial outputs + the left-over key, which is handled on the CUDA cores: a 64-long dot
 //              product per row) is deferred until the first block of tile t+1 has been handed to the tensor
 //              pipe, so no softmax warp ever waits for a P V product to retire.
-//   warp 8     TMA producer: K and V of the head (592 padded rows x 64, zero filled past 577 by the 3-D
-//              tensor map) once, then 128-row Q tiles into a double buffer
+//   warp 8     TMA producer: K and V of a head (576 rows x 64 in blocks of 96, each block re-loaded for the next
+//              head as soon as the current head's last product on it has retired; rows 576..591 -- key 576 and
+//              zero fill from the 3-D tensor map -- in a small double buffer), 128-row Q tiles into a double buffer
 //   warps 9/11 MMA issuer of group 0 / 1 (one thread each): S_n = Q K_n^T (M128 x N96 x K64, SS) into a double
 //              buffer, O_g += P_n V_n (TS form: P read from TMEM, V from shared memory as an MN-major operand)
 //   warp 10    TMEM allocator (2 groups x 2 x 96 columns for S / P, 2 x 64 for the partial outputs)
@@ -31,19 +33,20 @@ namespace at5 {
 constexpr int kS = EGPT_TOKENS;            // 577
 constexpr int kD = 64;
 constexpr int kHeads = 16;
-constexpr int kKeyPad = 592;
 constexpr int kQTile = 128;
 constexpr int kQTiles = (kS + kQTile - 1) / kQTile;      // 5
 constexpr int kBlk = 96;                                  // keys per block
-constexpr int kGroupKeys = 3 * kBlk;                      // 288: key group 0 = keys [0,288), group 1 = [288,592)
+constexpr int kGroupKeys = 3 * kBlk;                      // 288: key group 0 = keys [0,288), group 1 = [288,576)
 constexpr int kXKey = 2 * kGroupKeys;                     // 576: the left-over key, handled outside the MMAs
 constexpr int kNBlk = 3;                                  // blocks per group and tile
 constexpr int kThreads = 384;
 constexpr int kRowBytes = 128;                            // 64 bf16
-constexpr int kKVBytes = kKeyPad * kRowBytes;             // 75776
+constexpr int kKVBytes = kXKey * kRowBytes;               // 73728: 576 keys
 constexpr int kQBytes = kQTile * kRowBytes;               // 16384
+constexpr int kXBytes = 16 * kRowBytes;                   // rows 576..591 of K or V (key 576 + zero fill)
 constexpr int kSmemK = 0, kSmemV = kKVBytes, kSmemQ = 2 * kKVBytes;
-constexpr int kSmemBar = kSmemQ + 2 * kQBytes;
+constexpr int kSmemX = kSmemQ + 2 * kQBytes;              // [2 (head parity)][2 (K, V)][16 rows]
+constexpr int kSmemBar = kSmemX + 4 * kXBytes;
 constexpr int kSmemXch = kSmemBar + 512;                  // float [3 (max, sum, partial dot)][2 (tile parity)][2 (group)][128]
 constexpr int kSmemStage = kSmemXch + 6 * 1024;           // output staging: 8 warps x (32 rows x 64 B)
 constexpr int kStageBytes = 32 * 64;
@@ -51,13 +54,13 @@ constexpr int kSmemTotal = kSmemStage + 8 * kStageBytes + 1024;   // + alignment
 #ifndef EGPT_ATTN_STAGGER
 #define EGPT_ATTN_STAGGER 900
 #endif
-constexpr int kStagger = EGPT_ATTN_STAGGER;                             // cycles by which key group 1 starts behind group 0
+constexpr int kStagger = EGPT_ATTN_STAGGER;               // cycles by which key group 1 starts behind group 0
 constexpr int kTmemCols = 512;
 constexpr uint32_t kTmemS = 0, kTmemO = 4 * kBlk;         // columns: S/P [group][buffer][96], then O [group][64]
 #ifndef EGPT_ATTN_POLY_EVERY
 #define EGPT_ATTN_POLY_EVERY 4
 #endif
-constexpr int kPolyEvery = EGPT_ATTN_POLY_EVERY;                             // every kPolyEvery-th pair of exp2 runs as a cubic on the FMA pipe (0: none)
+constexpr int kPolyEvery = EGPT_ATTN_POLY_EVERY;          // every kPolyEvery-th pair of exp2 runs as a cubic on the FMA pipe (0: none)
 
 // MN-major B operand (V block: rows = keys (K), 64 contiguous dims (N) = 128 B per key, SWIZZLE_128B):
 // 8-key groups are 1024 B apart (SBO); a single 64-wide N block, so LBO is unused.
@@ -160,8 +163,9 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 }
 
 struct Bars {
-  uint64_t k_full[2][kNBlk], v_full[2][kNBlk];
-  uint64_t x_full;                       // rows 576..591 of K and V (the left-over key + zero fill)
+  uint64_t k_full[2][kNBlk], v_full[2][kNBlk];   // per head: a 96-key block of K / V landed
+  uint64_t k_free[2][kNBlk], v_free[2][kNBlk];   // per head: the head's last product on that block retired (commit)
+  uint64_t x_full[2], x_free[2];         // [head parity]: rows 576..591 of K and V landed / were last read (256 arrivals)
   uint64_t q_full[2], q_empty[2];        // Q tile double buffer; q_empty counts both issuers
   uint64_t s_full[2][2];                 // [group][buffer]: S block landed
   uint64_t p_full[2][2];                 // [group][buffer]: P stored over it by the group's 128 threads
@@ -182,12 +186,19 @@ __device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
   }
 }
 
+// Persistent: each CTA works through a contiguous range of (head, Q tile) units of the n_heads = frames x 16 (frame, head)
+// pairs.  Every barrier phase below is derived from running counters (it = head index inside this CTA's range, T = tile,
+// N = block), so the pipelines run straight across head boundaries: the next head's K / V / Q stream in while the last
+// tile of the current one is still in the softmax warps, and a head's last merge happens after the first block of the next.
 __global__ void __launch_bounds__(kThreads, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
-                    const __grid_constant__ CUtensorMap tmap_out, long long* __restrict__ trace) {
+                    const __grid_constant__ CUtensorMap tmap_out, int n_heads, long long* __restrict__ trace) {
   extern __shared__ uint8_t smem_raw[];
-#ifdef EGPT_ATTN_TRACE   // developer aid: clock64 phase stamps of CTA 0 (tools/attn_trace.py)
-#define TR(slot) do { if (trace != nullptr && blockIdx.x == 0) trace[(slot)] = clock64(); } while (0)
+#ifdef EGPT_ATTN_TRACE   // developer aid: clock64 phase stamps of CTA 0's first head (tools/attn_trace.py)
+#ifndef EGPT_ATTN_TRACE_IT
+#define EGPT_ATTN_TRACE_IT 0
+#endif
+#define TR(slot) do { if (trace != nullptr && blockIdx.x == 0 && it == EGPT_ATTN_TRACE_IT) trace[(slot)] = clock64(); } while (0)
 #else
 #define TR(slot) do { } while (0)
 #endif
@@ -195,18 +206,28 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   Bars* bars = reinterpret_cast<Bars*>(smem + kSmemBar);
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);    // warp-uniform by construction
   const int lane = threadIdx.x & 31;
-  const int f = blockIdx.x / kHeads, h = blockIdx.x % kHeads;
+  // This CTA's share: a contiguous range [g0, g1) of the n_heads * 5 (head, Q tile) units, so the load is even to within one
+  // tile; a head that straddles two CTAs has its K / V loaded by both.
+  const long long n_units = (long long)n_heads * kQTiles;
+  const int g0 = (int)(n_units * blockIdx.x / gridDim.x), g1 = (int)(n_units * (blockIdx.x + 1) / gridDim.x);
+  const int head0 = g0 / kQTiles, n_it = (g1 - 1) / kQTiles - head0 + 1;      // heads touched (>= 1)
+  // tiles [tb, te) of the it-th head of this CTA
+  auto tile_begin = [&](int it) { return it == 0 ? g0 - head0 * kQTiles : 0; };
+  auto tile_end = [&](int it) { return it == n_it - 1 ? g1 - (head0 + it) * kQTiles : kQTiles; };
 
   if (warp == 8 && lane == 0) { ptx::prefetch_tensormap(&tmap_q); ptx::prefetch_tensormap(&tmap_kv); ptx::prefetch_tensormap(&tmap_out); }
   if (warp == 9 && lane == 0) {
     for (int g = 0; g < 2; ++g) {
-      for (int i = 0; i < kNBlk; ++i) { ptx::mbar_init(&bars->k_full[g][i], 1); ptx::mbar_init(&bars->v_full[g][i], 1); }
+      for (int i = 0; i < kNBlk; ++i) {
+        ptx::mbar_init(&bars->k_full[g][i], 1); ptx::mbar_init(&bars->v_full[g][i], 1);
+        ptx::mbar_init(&bars->k_free[g][i], 1); ptx::mbar_init(&bars->v_free[g][i], 1);
+      }
+      ptx::mbar_init(&bars->x_full[g], 1); ptx::mbar_init(&bars->x_free[g], 256);
       ptx::mbar_init(&bars->q_full[g], 1); ptx::mbar_init(&bars->q_empty[g], 2);
       for (int i = 0; i < 2; ++i) {
         ptx::mbar_init(&bars->s_full[g][i], 1); ptx::mbar_init(&bars->p_full[g][i], 128); ptx::mbar_init(&bars->o_done[g][i], 1);
       }
     }
-    ptx::mbar_init(&bars->x_full, 1);
     ptx::mbar_init(&bars->o_free, 256);
     ptx::mbar_init(&bars->t_done, 258);
     ptx::fence_barrier_init();
@@ -224,39 +245,49 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
     if (warp == 8 && lane == 0) {
       // ===== TMA producer =====
-      auto load_q = [&](int t) {
-        uint8_t* dst = smem + kSmemQ + (t & 1) * kQBytes;
-        ptx::mbar_arrive_expect_tx(&bars->q_full[t & 1], kQBytes);
-        tma_load_3d(dst, &tmap_q, &bars->q_full[t & 1], h * kD, t * kQTile, f);
-        tma_load_3d(dst + 64 * kRowBytes, &tmap_q, &bars->q_full[t & 1], h * kD, t * kQTile + 64, f);
-      };
-      load_q(0);
-      // K then V, block by block and alternating between the two key groups (16-row boxes), so both groups' first
-      // MMAs can start before everything has landed
-      for (int kv = 0; kv < 2; ++kv) {
-        uint8_t* dst = smem + (kv == 0 ? kSmemK : kSmemV);
-        const int col = (kv + 1) * kHeads * kD + h * kD;
-        for (int j = 0; j < kNBlk; ++j)
-          for (int g = 0; g < 2; ++g) {
-            uint64_t* full = kv == 0 ? &bars->k_full[g][j] : &bars->v_full[g][j];
-            const int row0 = g * kGroupKeys + j * kBlk;
-            ptx::mbar_arrive_expect_tx(full, kBlk * kRowBytes);
-            for (int r = 0; r < kBlk; r += 16) tma_load_3d(dst + (row0 + r) * kRowBytes, &tmap_kv, full, col, row0 + r, f);
+      int T = 0;                                                       // tiles loaded so far
+      for (int it = 0; it < n_it; ++it) {
+        const int w = head0 + it, f = w / kHeads, h = w % kHeads;
+        const int tb = tile_begin(it), te = tile_end(it);
+        auto load_q = [&](int t) {
+          if (T >= 2) ptx::mbar_wait(&bars->q_empty[T & 1], (uint32_t)(((T >> 1) - 1) & 1));   // tile T-2's last Q K^T retired
+          uint8_t* dst = smem + kSmemQ + (T & 1) * kQBytes;
+          ptx::mbar_arrive_expect_tx(&bars->q_full[T & 1], kQBytes);
+          tma_load_3d(dst, &tmap_q, &bars->q_full[T & 1], h * kD, t * kQTile, f);
+          tma_load_3d(dst + 64 * kRowBytes, &tmap_q, &bars->q_full[T & 1], h * kD, t * kQTile + 64, f);
+          ++T;
+        };
+        load_q(tb);
+        // K then V, block by block and alternating between the two key groups (16-row boxes), each block as soon as the
+        // previous head has released it; the left-over key's rows right after the first K blocks (the softmax warps need
+        // them during their first block)
+        for (int kv = 0; kv < 2; ++kv) {
+          uint8_t* dst = smem + (kv == 0 ? kSmemK : kSmemV);
+          const int col = (kv + 1) * kHeads * kD + h * kD;
+          for (int j = 0; j < kNBlk; ++j) {
+            for (int g = 0; g < 2; ++g) {
+              uint64_t* full = kv == 0 ? &bars->k_full[g][j] : &bars->v_full[g][j];
+              if (it > 0) ptx::mbar_wait(kv == 0 ? &bars->k_free[g][j] : &bars->v_free[g][j], (uint32_t)((it - 1) & 1));
+              const int row0 = g * kGroupKeys + j * kBlk;
+              ptx::mbar_arrive_expect_tx(full, kBlk * kRowBytes);
+              for (int r = 0; r < kBlk; r += 16) tma_load_3d(dst + (row0 + r) * kRowBytes, &tmap_kv, full, col, row0 + r, f);
+            }
+            if (kv == 0 && j == 0) {
+              const int xs = it & 1;
+              if (it >= 2) ptx::mbar_wait(&bars->x_free[xs], (uint32_t)(((it >> 1) - 1) & 1));
+              uint8_t* xdst = smem + kSmemX + xs * 2 * kXBytes;
+              ptx::mbar_arrive_expect_tx(&bars->x_full[xs], 2 * kXBytes);
+              tma_load_3d(xdst, &tmap_kv, &bars->x_full[xs], kHeads * kD + h * kD, kXKey, f);
+              tma_load_3d(xdst + kXBytes, &tmap_kv, &bars->x_full[xs], 2 * kHeads * kD + h * kD, kXKey, f);
+            }
           }
-        if (kv == 0) {
-          load_q(1);
-          ptx::mbar_arrive_expect_tx(&bars->x_full, 2 * 16 * kRowBytes);
-          tma_load_3d(smem + kSmemK + kXKey * kRowBytes, &tmap_kv, &bars->x_full, kHeads * kD + h * kD, kXKey, f);
-          tma_load_3d(smem + kSmemV + kXKey * kRowBytes, &tmap_kv, &bars->x_full, 2 * kHeads * kD + h * kD, kXKey, f);
+          if (kv == 0 && tb + 1 < te) load_q(tb + 1);
         }
-      }
-      for (int t = 2; t < kQTiles; ++t) {
-        ptx::mbar_wait(&bars->q_empty[t & 1], (uint32_t)(((t >> 1) - 1) & 1));   // both groups' last Q K^T of tile t-2 retired
-        load_q(t);
+        for (int t = tb + 2; t < te; ++t) load_q(t);
       }
     } else if (warp == 9 || warp == 11) {
       // ===== MMA issuer of key group gi: an independent in-order stream of S and P V products.  The whole warp walks the
-      // loop (uniform control flow and operands); one elected lane issues =====
+      // loop (uniform control flow and operands, so descriptors live in uniform registers); one elected lane issues =====
       const int gi = warp == 9 ? 0 : 1;
       const uint64_t dK0 = ptx::make_smem_desc_sw128(ptx::smem_u32(smem + kSmemK + gi * kGroupKeys * kRowBytes));
       const uint64_t dV0 = make_desc_mn_sw128(ptx::smem_u32(smem + kSmemV + gi * kGroupKeys * kRowBytes));
@@ -265,14 +296,15 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       const uint32_t tmem_o = tmem_base + kTmemO + (uint32_t)(gi * kD);
       constexpr uint32_t idesc_pv = idesc_bf16(kQTile, kD, 1);
       constexpr uint32_t idesc_s = idesc_bf16(kQTile, kBlk, 0);
-      auto issue_pv = [&](int n) {
-        const int t = n / kNBlk, j = n - t * kNBlk, b = n & 1;
-        if (n < kNBlk) ptx::mbar_wait(&bars->v_full[gi][j], 0);
-        TR(1024 + gi * 256 + n * 8 + 2);
-        ptx::mbar_wait(&bars->p_full[gi][b], (uint32_t)((n >> 1) & 1));
-        TR(1024 + gi * 256 + n * 8 + 3);
+      // P V of block N: head it of this CTA, local tile counter T, block j; first / last = the head's first / last tile here
+      auto issue_pv = [&](int N, int it, int T, int j, bool first, bool last) {
+        const int b = N & 1;
+        if (first) ptx::mbar_wait(&bars->v_full[gi][j], (uint32_t)(it & 1));
+        TR(2048 + gi * 256 + (N % 16) * 8 + 2);
+        ptx::mbar_wait(&bars->p_full[gi][b], (uint32_t)((N >> 1) & 1));
+        TR(2048 + gi * 256 + (N % 16) * 8 + 3);
         // the first block of a tile overwrites the accumulator: the previous tile's output must have been read out
-        if (j == 0 && t > 0) ptx::mbar_wait(&bars->o_free, (uint32_t)((t - 1) & 1));
+        if (j == 0 && T > 0) ptx::mbar_wait(&bars->o_free, (uint32_t)((T - 1) & 1));
         ptx::tcgen05_fence_after();
         const uint32_t tmem_p = tmem_s0 + (uint32_t)(b * kBlk);
         // A = P from TMEM: 16 keys = 8 packed columns per k-step; B = V rows 16*kk .. +15 of the block (2048 B = 128 units)
@@ -283,34 +315,42 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             umma_bf16_ts(tmem_o, tmem_p + (uint32_t)(kk * 8), dv + (uint64_t)(kk * 128), idesc_pv, (j != 0 || kk != 0) ? 1u : 0u);
           ptx::umma_commit(&bars->o_done[gi][b]);
           if (j == kNBlk - 1) ptx::umma_commit(&bars->t_done);
+          if (last) ptx::umma_commit(&bars->v_free[gi][j]);                  // the head's last use of this V block
         }
         __syncwarp();
-        TR(1024 + gi * 256 + n * 8 + 4);
+        TR(2048 + gi * 256 + (N % 16) * 8 + 4);
       };
-      int n = 0;
-      for (int t = 0; t < kQTiles; ++t) {
-        ptx::mbar_wait(&bars->q_full[t & 1], (uint32_t)((t >> 1) & 1));
-        const uint64_t dq = dQ0 + (uint64_t)((t & 1) * (kQBytes >> 4));
-        for (int j = 0; j < kNBlk; ++j, ++n) {
-          if (t == 0) ptx::mbar_wait(&bars->k_full[gi][j], 0);
-          TR(1024 + gi * 256 + n * 8 + 0);
-          // S_n overwrites the buffer that held P_{n-2}; P V of block n-2 was issued earlier by this same thread and
-          // the tensor pipe runs one thread's MMAs in issue order, so that reuse needs no barrier.
-          ptx::tcgen05_fence_after();
-          const uint32_t tmem_s = tmem_s0 + (uint32_t)((n & 1) * kBlk);
-          const uint64_t dk = dK0 + (uint64_t)(j * (kBlk * kRowBytes >> 4));
-          if (ptx::elect_one()) {
+      int N = 0, T = 0;
+      int p_it = 0, p_T = 0, p_j = 0;                                  // block N-1, whose P V is still to be issued
+      bool p_first = false, p_last = false;
+      for (int it = 0; it < n_it; ++it) {
+        const int tb = tile_begin(it), te = tile_end(it);
+        for (int t = tb; t < te; ++t, ++T) {
+          ptx::mbar_wait(&bars->q_full[T & 1], (uint32_t)((T >> 1) & 1));
+          const uint64_t dq = dQ0 + (uint64_t)((T & 1) * (kQBytes >> 4));
+          for (int j = 0; j < kNBlk; ++j, ++N) {
+            if (t == tb) ptx::mbar_wait(&bars->k_full[gi][j], (uint32_t)(it & 1));
+            TR(2048 + gi * 256 + (N % 16) * 8 + 0);
+            // S_N overwrites the buffer that held P_{N-2}; P V of block N-2 was issued earlier by this same thread and
+            // the tensor pipe runs one thread's MMAs in issue order, so that reuse needs no barrier.
+            ptx::tcgen05_fence_after();
+            const uint32_t tmem_s = tmem_s0 + (uint32_t)((N & 1) * kBlk);
+            const uint64_t dk = dK0 + (uint64_t)(j * (kBlk * kRowBytes >> 4));
+            if (ptx::elect_one()) {
 #pragma unroll
-            for (int k = 0; k < kD / 16; ++k) ptx::umma_bf16_ss(tmem_s, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc_s, k != 0);
-            ptx::umma_commit(&bars->s_full[gi][n & 1]);
-            if (j == kNBlk - 1) ptx::umma_commit(&bars->q_empty[t & 1]);
+              for (int k = 0; k < kD / 16; ++k) ptx::umma_bf16_ss(tmem_s, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc_s, k != 0);
+              ptx::umma_commit(&bars->s_full[gi][N & 1]);
+              if (j == kNBlk - 1) ptx::umma_commit(&bars->q_empty[T & 1]);
+              if (t == te - 1) ptx::umma_commit(&bars->k_free[gi][j]);       // the head's last use of this K block
+            }
+            __syncwarp();
+            TR(2048 + gi * 256 + (N % 16) * 8 + 1);
+            if (N >= 1) issue_pv(N - 1, p_it, p_T, p_j, p_first, p_last);
+            p_it = it; p_T = T; p_j = j; p_first = (t == tb); p_last = (t == te - 1);
           }
-          __syncwarp();
-          TR(1024 + gi * 256 + n * 8 + 1);
-          if (n >= 1) issue_pv(n - 1);
         }
       }
-      issue_pv(n - 1);
+      issue_pv(N - 1, p_it, p_T, p_j, p_first, p_last);
     }
   } else {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
@@ -324,28 +364,29 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     const uint32_t tmem_o_other = tmem_base + lane_base + kTmemO + (uint32_t)((gi ^ 1) * kD);
     float* xch = reinterpret_cast<float*>(smem + kSmemXch);           // [3][2 (tile parity)][2 (group)][128]
     constexpr float kLog2e = 1.4426950408889634f;
-    const bool trc = (q == 0 && lane == 0);
     float m = -INFINITY, l = 0.f;
     float dot_cur = 0.f;                                               // this thread's half of q_r . k_576 for the tile
 
-    // Merge of tile tp: the two groups' (max, sum, partial output) and the left-over key 576, whose score is the sum of
-    // the two threads' partial dot products.  Each thread finishes 32 of the 64 output dims.
-    auto publish = [&](int tp) {                                       // at the end of the tile's last block
-      float* x_t = xch + (tp & 1) * 256;
+    auto publish = [&](int T) {                                        // at the end of the tile's last block
+      float* x_t = xch + (T & 1) * 256;
       x_t[gi * 128 + r] = m;
       x_t[512 + gi * 128 + r] = l;
       x_t[1024 + gi * 128 + r] = dot_cur;
       ptx::mbar_arrive(&bars->t_done);
     };
-    auto merge = [&](int tp) {
-      [[maybe_unused]] const int last = tp * kNBlk + kNBlk - 1;      // trace slot
-      const float* x_t = xch + (tp & 1) * 256;
+    // Merge of local tile T (tile tp of this CTA's it-th head): the two groups' (max, sum, partial output) and the left-over
+    // key 576, whose score is the sum of the two threads' partial dot products.  Each thread finishes 32 of the 64 dims.
+    auto merge = [&](int T, int it, int tp, bool head_done) {
+      const int w = head0 + it, f = w / kHeads, h = w % kHeads;
+      const bool trc = (lane == 0);
+      [[maybe_unused]] const int last = (T % 5) * kNBlk + kNBlk - 1;   // trace slot
+      const float* x_t = xch + (T & 1) * 256;
       const float m_me = x_t[gi * 128 + r], l_me = x_t[512 + gi * 128 + r];
       // The partner group runs on its own clock.  One barrier covers everything this merge needs from it and from the
       // tensor pipe; it cannot run a phase ahead because the next tile's P V products wait for o_free, released below.
-      if (trc) TR(gi * 512 + last * 16 + 10);
-      ptx::mbar_wait(&bars->t_done, (uint32_t)(tp & 1));
-      if (trc) TR(gi * 512 + last * 16 + 7);
+      if (trc) TR(warp * 256 + last * 16 + 10);
+      ptx::mbar_wait(&bars->t_done, (uint32_t)(T & 1));
+      if (trc) TR(warp * 256 + last * 16 + 7);
       const float mo = x_t[(gi ^ 1) * 128 + r], lo = x_t[512 + (gi ^ 1) * 128 + r];
       const float sx = (x_t[1024 + gi * 128 + r] + x_t[1024 + (gi ^ 1) * 128 + r]) * kLog2e;
       ptx::tcgen05_fence_after();
@@ -355,7 +396,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       ptx::tmem_ld_wait();
       ptx::tcgen05_fence_before();
       ptx::mbar_arrive(&bars->o_free);
-      if (trc) TR(gi * 512 + last * 16 + 8);
+      if (trc) TR(warp * 256 + last * 16 + 8);
       const float mt = fmaxf(fmaxf(m_me, mo), sx);
       const float fa = ex2(m_me - mt), fb = ex2(mo - mt), px = ex2(sx - mt);
       const float inv = __fdividef(1.0f, fmaf(l_me, fa, lo * fb) + px);
@@ -364,144 +405,153 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       uint8_t* stage = smem + kSmemStage + warp * kStageBytes;
       if (lane == 0) ptx::bulk_wait_group_read<0>();                   // the previous tile's store has read the slab
       __syncwarp();
-      const uint4* vx = reinterpret_cast<const uint4*>(smem + kSmemV + kXKey * kRowBytes) + gi * 4;   // row 576: unswizzled
+      const uint4* vx = reinterpret_cast<const uint4*>(smem + kSmemX + (it & 1) * 2 * kXBytes + kXBytes) + gi * 4;   // V row 576
       const float2 ca2 = make_float2(ca, ca), cb2 = make_float2(cb, cb), cx2 = make_float2(cx, cx), z2 = make_float2(0.f, 0.f);
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         float vf[8];
         unpack8(vx[c], vf);
-        uint32_t w[4];
+        uint32_t wd[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           float2 e = ffma2(make_float2(vf[2 * i], vf[2 * i + 1]), cx2, z2);
           e = ffma2(make_float2(__uint_as_float(ob[8 * c + 2 * i]), __uint_as_float(ob[8 * c + 2 * i + 1])), cb2, e);
           e = ffma2(make_float2(__uint_as_float(oa[8 * c + 2 * i]), __uint_as_float(oa[8 * c + 2 * i + 1])), ca2, e);
-          w[i] = pack2(e.x, e.y);
+          wd[i] = pack2(e.x, e.y);
         }
-        *reinterpret_cast<uint4*>(stage + lane * 64 + c * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+        *reinterpret_cast<uint4*>(stage + lane * 64 + c * 16) = make_uint4(wd[0], wd[1], wd[2], wd[3]);
       }
-      if (trc) TR(gi * 512 + last * 16 + 13);
+      if (head_done) ptx::mbar_arrive(&bars->x_free[it & 1]);          // the head's rows 576.. are no longer needed
+      if (trc) TR(warp * 256 + last * 16 + 13);
       ptx::fence_proxy_async();
       __syncwarp();
       if (lane == 0) {
         tma_store_3d(&tmap_out, stage, h * kD + gi * 32, tp * kQTile + q * 32, f);
         ptx::bulk_commit_group();
       }
-      if (trc) TR(gi * 512 + last * 16 + 9);
+      if (trc) TR(warp * 256 + last * 16 + 9);
     };
 
-    ptx::mbar_wait(&bars->x_full, 0);
-    if (gi == 1) {
-      // Run the two key groups out of phase: while one is in its exp2 stretch (MUFU bound) the other loads, reduces, merges
-      // or waits.  Nothing below re-aligns them: the groups only meet through mbarriers that are long complete when polled.
-      ptx::mbar_wait(&bars->s_full[1][0], 0);
-      const long long t0 = clock64();
-      while (clock64() - t0 < kStagger) { }
-    }
-    int n = 0;
-    for (int t = 0; t < kQTiles; ++t) {
-      for (int j = 0; j < kNBlk; ++j, ++n) {
-        const int b = n & 1;
-        const uint32_t ts = tmem_s0 + (uint32_t)(b * kBlk);
-        if (trc) TR(gi * 512 + n * 16 + 0);
-        ptx::mbar_wait(&bars->s_full[gi][b], (uint32_t)((n >> 1) & 1));
-        ptx::tcgen05_fence_after();
-        if (trc) TR(gi * 512 + n * 16 + 1);
-        uint32_t v[3][32];
-        ptx::tmem_ld_32x32b_x32(ts, v[0]);
-        ptx::tmem_ld_32x32b_x32(ts + 32u, v[1]);
-        ptx::tmem_ld_32x32b_x32(ts + 64u, v[2]);
-        float dot = 0.f;
-        if (j == 0) {
-          // this thread's half of q_r . k_576, while the TMEM load is in flight.  The Q tile stays put until both
-          // issuers have committed the tile's last S product, which cannot happen before this thread hands over P of
-          // this very block; the wait below is only the acquire on the TMA-written tile.
-          ptx::mbar_wait(&bars->q_full[t & 1], (uint32_t)((t >> 1) & 1));
-          const uint8_t* qrow = smem + kSmemQ + (t & 1) * kQBytes + r * kRowBytes;
-          const uint4* kx = reinterpret_cast<const uint4*>(smem + kSmemK + kXKey * kRowBytes) + gi * 4;
-          float d4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            float qf[8], kf[8];
-            unpack8(*reinterpret_cast<const uint4*>(qrow + (((gi * 4 + c) ^ (r & 7)) << 4)), qf);
-            unpack8(kx[c], kf);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) d4[i & 3] = fmaf(qf[i], kf[i], d4[i & 3]);
+    int N = 0, T = 0;
+    int m_it = 0, m_tp = 0;                                            // tile T-1, whose merge is still to be done
+    bool m_done = false;
+    for (int it = 0; it < n_it; ++it) {
+      const bool trc = (lane == 0);
+      const int tb = tile_begin(it), te = tile_end(it);
+      for (int t = tb; t < te; ++t, ++T) {
+        for (int j = 0; j < kNBlk; ++j, ++N) {
+          const int b = N & 1;
+          [[maybe_unused]] const int n = N % 16;                        // trace slot
+          const uint32_t ts = tmem_s0 + (uint32_t)(b * kBlk);
+          if (trc) TR(warp * 256 + n * 16 + 0);
+          ptx::mbar_wait(&bars->s_full[gi][b], (uint32_t)((N >> 1) & 1));
+          if (gi == 1 && t == tb && j == 0) {
+            // Run the two key groups out of phase: while one is in its exp2 stretch (MUFU bound) the other loads, reduces,
+            // merges or waits.  Both groups meet at a head's first S block (they wait for the same K / Q loads), so the
+            // offset is re-established there; in between they only share mbarriers that are long complete when polled.
+            const long long t0 = clock64();
+            while (clock64() - t0 < kStagger) { }
           }
-          dot = (d4[0] + d4[1]) + (d4[2] + d4[3]);
-        }
-        ptx::tmem_ld_wait();
-        if (trc) TR(gi * 512 + n * 16 + 2);
-        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+          ptx::tcgen05_fence_after();
+          if (trc) TR(warp * 256 + n * 16 + 1);
+          uint32_t v[3][32];
+          ptx::tmem_ld_32x32b_x32(ts, v[0]);
+          ptx::tmem_ld_32x32b_x32(ts + 32u, v[1]);
+          ptx::tmem_ld_32x32b_x32(ts + 64u, v[2]);
+          float dot = 0.f;
+          if (j == 0) {
+            // this thread's half of q_r . k_576, while the TMEM load is in flight.  The Q tile stays put until both
+            // issuers have committed the tile's last S product, which cannot happen before this thread hands over P of
+            // this very block; the waits below are only the acquire on the TMA-written data.
+            ptx::mbar_wait(&bars->q_full[T & 1], (uint32_t)((T >> 1) & 1));
+            if (t == tb) ptx::mbar_wait(&bars->x_full[it & 1], (uint32_t)((it >> 1) & 1));
+            const uint8_t* qrow = smem + kSmemQ + (T & 1) * kQBytes + r * kRowBytes;
+            const uint4* kx = reinterpret_cast<const uint4*>(smem + kSmemX + (it & 1) * 2 * kXBytes) + gi * 4;   // K row 576
+            float d4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int c = 0; c < 3; ++c)
+            for (int c = 0; c < 4; ++c) {
+              float qf[8], kf[8];
+              unpack8(*reinterpret_cast<const uint4*>(qrow + (((gi * 4 + c) ^ (r & 7)) << 4)), qf);
+              unpack8(kx[c], kf);
 #pragma unroll
-          for (int i = 0; i < 32; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(v[c][i]));
-        const float m_blk = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * kLog2e;   // exp2 domain; finite
-        if (j == 0) {
-          m = m_blk; l = 0.f;                                          // fresh accumulator, nothing to rescale
-        } else {
-          // Lazy rescale: only when this block raises the row maximum by more than 2^8 are the accumulator and the
-          // running sum moved to the new frame; otherwise the stale maximum stays and p may reach 256.
-          const bool need = m_blk - m > 8.0f;
-          if (__any_sync(0xffffffffu, need)) {
-            const float fac = need ? ex2(m - m_blk) : 1.0f;
-            // P V of block n-1 must have retired (blocks <= n-2 have: S_n was committed after them, so this barrier is
-            // at most one phase behind and the parity wait is exact)
-            ptx::mbar_wait(&bars->o_done[gi][(n - 1) & 1], (uint32_t)(((n - 1) >> 1) & 1));
-            ptx::tcgen05_fence_after();
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {
-              uint32_t a[32];
-              ptx::tmem_ld_32x32b_x32(tmem_o + (uint32_t)(32 * c), a);
-              ptx::tmem_ld_wait();
-#pragma unroll
-              for (int i = 0; i < 32; ++i) a[i] = __float_as_uint(__uint_as_float(a[i]) * fac);
-              tmem_st_32x32b_x16(tmem_o + (uint32_t)(32 * c), a);
-              tmem_st_32x32b_x16(tmem_o + (uint32_t)(32 * c + 16), a + 16);
+              for (int i = 0; i < 8; ++i) d4[i & 3] = fmaf(qf[i], kf[i], d4[i & 3]);
             }
-            l *= fac;
-            if (need) m = m_blk;
+            dot = (d4[0] + d4[1]) + (d4[2] + d4[3]);
           }
-        }
-        if (trc) TR(gi * 512 + n * 16 + 3);
-        // exp2 on packed fp32x2 instructions (FFMA2 / FADD2): scale, cubic and row sum cost half the issue slots
-        float2 s2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
-        const float2 sc = make_float2(kLog2e, kLog2e), nm = make_float2(-m, -m);
+          ptx::tmem_ld_wait();
+          if (trc) TR(warp * 256 + n * 16 + 2);
+          float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          uint32_t w[16];
+          for (int c = 0; c < 3; ++c)
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const float2 x = ffma2(make_float2(__uint_as_float(v[c][2 * i]), __uint_as_float(v[c][2 * i + 1])), sc, nm);
-            float2 p;
-            if (kPolyEvery > 0 && (i % (kPolyEvery > 0 ? kPolyEvery : 1)) == kPolyEvery - 1) {
-              p = ex2_poly2(x);
-            } else {
-              p.x = ex2(x.x); p.y = ex2(x.y);
+            for (int i = 0; i < 32; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(v[c][i]));
+          const float m_blk = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * kLog2e;   // exp2 domain; finite
+          if (j == 0) {
+            m = m_blk; l = 0.f;                                        // fresh accumulator, nothing to rescale
+          } else {
+            // Lazy rescale: only when this block raises the row maximum by more than 2^8 are the accumulator and the
+            // running sum moved to the new frame; otherwise the stale maximum stays and p may reach 256.
+            const bool need = m_blk - m > 8.0f;
+            if (__any_sync(0xffffffffu, need)) {
+              const float fac = need ? ex2(m - m_blk) : 1.0f;
+              // P V of block N-1 must have retired (blocks <= N-2 have: S_N was committed after them, so this barrier is
+              // at most one phase behind and the parity wait is exact)
+              ptx::mbar_wait(&bars->o_done[gi][(N - 1) & 1], (uint32_t)(((N - 1) >> 1) & 1));
+              ptx::tcgen05_fence_after();
+#pragma unroll
+              for (int c = 0; c < 2; ++c) {
+                uint32_t a[32];
+                ptx::tmem_ld_32x32b_x32(tmem_o + (uint32_t)(32 * c), a);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) a[i] = __float_as_uint(__uint_as_float(a[i]) * fac);
+                tmem_st_32x32b_x16(tmem_o + (uint32_t)(32 * c), a);
+                tmem_st_32x32b_x16(tmem_o + (uint32_t)(32 * c + 16), a + 16);
+              }
+              l *= fac;
+              if (need) m = m_blk;
             }
-            s2[i & 1] = fadd2(s2[i & 1], p);
-            w[i] = pack2(p.x, p.y);
           }
-          tmem_st_32x32b_x16(ts + (uint32_t)(16 * c), w);             // P over S: column c <- keys 2c, 2c+1
-        }
-        l += (s2[0].x + s2[0].y) + (s2[1].x + s2[1].y);
-        if (trc) TR(gi * 512 + n * 16 + 4);
-        tmem_st_wait();
-        ptx::tcgen05_fence_before();
-        ptx::mbar_arrive(&bars->p_full[gi][b]);
-        if (trc) TR(gi * 512 + n * 16 + 5);
-        if (j == 0) {
-          // With this tile's first block handed to the tensor pipe, finish the previous tile: its last P V has had a whole
-          // block's time to retire, so the waits inside return at once.
-          if (t > 0) merge(t - 1);
-          dot_cur = dot;
-        } else if (j == kNBlk - 1) {
-          publish(t);
+          if (trc) TR(warp * 256 + n * 16 + 3);
+          // exp2 on packed fp32x2 instructions (FFMA2 / FADD2): scale, cubic and row sum cost half the issue slots
+          float2 s2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+          const float2 sc = make_float2(kLog2e, kLog2e), nm = make_float2(-m, -m);
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            uint32_t wd[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float2 x = ffma2(make_float2(__uint_as_float(v[c][2 * i]), __uint_as_float(v[c][2 * i + 1])), sc, nm);
+              float2 pp;
+              if (kPolyEvery > 0 && (i % (kPolyEvery > 0 ? kPolyEvery : 1)) == kPolyEvery - 1) {
+                pp = ex2_poly2(x);
+              } else {
+                pp.x = ex2(x.x); pp.y = ex2(x.y);
+              }
+              s2[i & 1] = fadd2(s2[i & 1], pp);
+              wd[i] = pack2(pp.x, pp.y);
+            }
+            tmem_st_32x32b_x16(ts + (uint32_t)(16 * c), wd);          // P over S: column c <- keys 2c, 2c+1
+          }
+          l += (s2[0].x + s2[0].y) + (s2[1].x + s2[1].y);
+          if (trc) TR(warp * 256 + n * 16 + 4);
+          tmem_st_wait();
+          ptx::tcgen05_fence_before();
+          ptx::mbar_arrive(&bars->p_full[gi][b]);
+          if (trc) TR(warp * 256 + n * 16 + 5);
+          if (j == 0) {
+            // With this tile's first block handed to the tensor pipe, finish the previous tile (possibly the previous head's
+            // last one): its last P V has had a whole block's time to retire, so the wait inside returns at once.
+            if (T > 0) merge(T - 1, m_it, m_tp, m_done);
+            m_it = it; m_tp = t; m_done = (t == te - 1);
+            dot_cur = dot;
+          } else if (j == kNBlk - 1) {
+            publish(T);
+          }
         }
       }
     }
-    merge(kQTiles - 1);
+    merge(T - 1, m_it, m_tp, m_done);
     if (lane == 0) ptx::bulk_wait_group_read<0>();
   }
 
@@ -558,7 +608,8 @@ int attention_impl(const void* qkv, int n_frames_total, void* out, cudaStream_t 
   // per launch: the attribute is per device, and one process may drive several GPUs
   EGPT_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
   ProfScope prof(PROF_ATTN, 4.0 * kS * kS * kD * kHeads * (double)n_frames_total, stream);
-  attention_tc_kernel<<<n_frames_total * kHeads, kThreads, kSmemTotal, stream>>>(tm_q, tm_kv, tm_out, trace);
+  const int n_heads = n_frames_total * kHeads, n_units = n_heads * kQTiles;
+  attention_tc_kernel<<<n_units < kNumSMs ? n_units : kNumSMs, kThreads, kSmemTotal, stream>>>(tm_q, tm_kv, tm_out, n_heads, trace);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
 }
@@ -570,8 +621,8 @@ int attention(const void* qkv, int n_frames_total, void* out, cudaStream_t strea
 }  // namespace egpt
 
 #ifdef EGPT_ATTN_TRACE
-// developer aid (tools/attn_trace.py): clock64 stamps of CTA 0 -- softmax warps 0 / 4 lane 0 at trace[group*512 + n*16 + k],
-// the two MMA issuers at trace[1024 + group*256 + n*8 + k]
+// developer aid (tools/attn_trace.py): clock64 stamps of CTA 0 -- lane 0 of softmax warp w at trace[w*256 + n*16 + k],
+// the two MMA issuers at trace[2048 + group*256 + n*8 + k]
 extern "C" int egpt_attention_trace(const uint16_t* qkv, int n_frames_total, uint16_t* out, long long* trace, void* stream) {
   return egpt::attention_impl(qkv, n_frames_total, out, (cudaStream_t)stream, trace);
 }

@@ -139,7 +139,7 @@ def stage_attn():
         leg = lib().egpt_attention_legacy
         leg.restype, leg.argtypes = C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         fns["legacy"] = leg
-    for F in (1, 3):
+    for F in (1, 3, 37, 160):                    # 37 / 160 frames: several heads per persistent CTA
         qkv = (torch.randn(F * 577, 3072, device=dev)).bfloat16()
         q, k, v = (qkv.float().view(F, 577, 3, 16, 64)[:, :, i].transpose(1, 2) for i in range(3))
         ref = (torch.softmax(q @ k.transpose(-1, -2), -1) @ v).transpose(1, 2).reshape(F * 577, 1024)
