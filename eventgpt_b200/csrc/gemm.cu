@@ -77,8 +77,11 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t rank = ptx::cluster_ctarank();
+  // warp index and CTA rank are made warp-uniform by construction: the producer and MMA warps then run their loops with
+  // uniform control flow and operands (descriptors, coordinates and barrier addresses in uniform registers) and only the
+  // TMA / MMA instructions themselves sit under elect.sync
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+  const uint32_t rank = __shfl_sync(0xffffffffu, ptx::cluster_ctarank(), 0);
   const bool leader = rank == 0;
   const int n_tiles = N / BN;
   const long long m_pairs = (M + 2 * BM - 1) / (2 * BM);
@@ -103,9 +106,9 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   ptx::tcgen05_fence_before();
   ptx::cluster_sync_all();                                  // barriers of both CTAs initialised before anyone signals them
   ptx::tcgen05_fence_after();
-  const uint32_t tmem_base = *tmem_ptr;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_ptr, 0);
 
-  if (warp == 0 && lane == 0) {
+  if (warp == 0) {
     // ===== TMA producer (both CTAs) =====
     int stage = 0; uint32_t phase = 0;
     for (long long tile = first; tile < num_tiles; tile += step) {
@@ -114,13 +117,16 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       for (int kb = 0; kb < num_kb; ++kb) {
         ptx::mbar_wait(empty_bar + stage, phase ^ 1);
         uint8_t* sa = smem + stage * kStageBytes2;
-        if (leader) ptx::mbar_arrive_expect_tx(full_bar + stage, 2 * kStageBytes2);   // bytes of both CTAs
-        ptx::tma_load_2d_2sm(sa, &tmap_a, full_bar + stage, kb * BK, m0);
-        ptx::tma_load_2d_2sm(sa + kABytes, &tmap_b, full_bar + stage, kb * BK, n0);
+        if (ptx::elect_one()) {
+          if (leader) ptx::mbar_arrive_expect_tx(full_bar + stage, 2 * kStageBytes2);   // bytes of both CTAs
+          ptx::tma_load_2d_2sm(sa, &tmap_a, full_bar + stage, kb * BK, m0);
+          ptx::tma_load_2d_2sm(sa + kABytes, &tmap_b, full_bar + stage, kb * BK, n0);
+        }
+        __syncwarp();
         if (++stage == kStages2) { stage = 0; phase ^= 1; }
       }
     }
-  } else if (warp == 1 && lane == 0 && leader) {
+  } else if (warp == 1 && leader) {
     // ===== MMA issuer (leader CTA only) =====
     constexpr uint32_t idesc = ptx::make_idesc_bf16(2 * BM, BN);
     int stage = 0; uint32_t phase = 0;
@@ -134,13 +140,16 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         ptx::tcgen05_fence_after();
         const uint32_t sa = ptx::smem_u32(smem + stage * kStageBytes2);
         const uint64_t da = ptx::make_smem_desc_sw128(sa), db = ptx::make_smem_desc_sw128(sa + kABytes);
+        if (ptx::elect_one()) {
 #pragma unroll
-        for (int k = 0; k < BK / UMMA_K; ++k)
-          ptx::umma_bf16_ss_2sm(tmem_d, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
-        ptx::umma_commit_2sm(empty_bar + stage);              // both producers may refill this slot
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            ptx::umma_bf16_ss_2sm(tmem_d, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+          ptx::umma_commit_2sm(empty_bar + stage);            // both producers may refill this slot
+          if (kb == num_kb - 1) ptx::umma_commit_2sm(tmem_full + acc);   // both epilogues may read their accumulator half
+        }
+        __syncwarp();
         if (++stage == kStages2) { stage = 0; phase ^= 1; }
       }
-      ptx::umma_commit_2sm(tmem_full + acc);                  // both epilogues may read their accumulator half
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else if (warp >= 4) {
