@@ -76,6 +76,36 @@ def test_attention_vs_fp32_reference(dev):
     assert _cos(out.float(), ref) > 0.9999
 
 
+@pytest.mark.parametrize("F", [1, 2, 7, 38])
+def test_attention_persistent_ranges(F, dev):
+    """The attention kernel is persistent: each of (at most) 148 CTAs walks a contiguous range of (frame, head, Q tile) units.
+    F = 1: fewer units than SMs, one tile per CTA; F = 2: ranges of one or two tiles that straddle heads; F = 7: 3-4 tiles, most
+    CTAs start mid-head; F = 38: ~20 tiles = four heads per CTA (shared-memory and TMEM reuse across heads, the deferred merge
+    of a head's last tile, double-buffered rows of the left-over key).  Heads get different score scales, and the key that is
+    handled outside the MMAs (576) is made the dominant one for some rows."""
+    from eventgpt_b200 import events as E
+    from eventgpt_b200._lib import lib, check
+    g = torch.Generator(device="cpu").manual_seed(100 + F)
+    qkv = torch.randn(F, 577, 3, 16, 64, generator=g)
+    qkv[:, :, 0] *= torch.linspace(0.2, 1.5, 16)[None, None, :, None]         # per-head temperature
+    qkv[:, 576, 1, 3] = qkv[:, 100, 0, 3] * 3.0                                # head 3: key 576 dominates row 100 (and friends)
+    x = qkv.reshape(F * 577, 3072).bfloat16().to(dev)
+    out = torch.full((F * 577, 1024), float("nan"), device=dev, dtype=torch.bfloat16)
+    check(lib().egpt_attention(E.ptr(x), F, E.ptr(out), E.stream_ptr(dev)), "attention")
+    xf = x.float().view(F, 577, 3, 16, 64)
+    q, k, v = (xf[:, :, i].transpose(1, 2) for i in range(3))
+    p = torch.softmax(q @ k.transpose(-1, -2), -1)
+    assert p[:, 3, 100, 576].min().item() > 0.5                                # the left-over key really matters there
+    ref = (p @ v).transpose(1, 2).reshape(F * 577, 1024)
+    assert torch.isfinite(out.float()).all()
+    assert (out.float() - ref).abs().max().item() < 3e-2
+    assert _cos(out.float(), ref) > 0.9999
+    # a second launch on the same buffers gives the same bits (no state carried between launches)
+    out2 = torch.empty_like(out)
+    check(lib().egpt_attention(E.ptr(x), F, E.ptr(out2), E.stream_ptr(dev)), "attention")
+    assert torch.equal(out, out2)
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_get_spatio_temporal_features(dtype, dev):
     """model/EventChatModel.py:15-38 incl. zero padding / truncation of the temporal tokens."""
