@@ -27,10 +27,10 @@ METRIC = "event_windows_per_s_to_visual_tokens"
 UNIT = "windows/s"
 H, W = 480, 640
 EVENTS_PER_WINDOW = 1_000_000
-BATCH_PER_GPU = 32
+BATCH_PER_GPU = int(os.environ.get("EGPT_BENCH_BATCH", "32"))     # windows per GPU and step (BASELINE configs[1]: 32); the override is a tuning aid
 N_FRAMES = 5
 GFLOP_PER_WINDOW = 2127.4            # tower 1909.6 + projector 121.0 + adaptor 96.8 (reference op order)
-WORKLOAD = "synthetic 50 ms windows, 1M events at 640x480, batch 32 per GPU, bf16 (BASELINE configs[1])"
+WORKLOAD = f"synthetic 50 ms windows, 1M events at 640x480, batch {BATCH_PER_GPU} per GPU, bf16 (BASELINE configs[1])"
 
 
 def synth_window(global_index, n_events=EVENTS_PER_WINDOW, h=H, w=W):
