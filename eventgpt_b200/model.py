@@ -315,6 +315,25 @@ class EventGPTVisualFrontEnd:
         pos, am, emb, lab = splice_event_features(embed_table, input_ids, position_ids, attention_mask, labels, event_features)
         return None, pos, am, past_key_values, emb, lab
 
+    def generate(self, embed_table, inputs=None, event_tensors=None, event_image_sizes=None, event_features=None, llm=None,
+                 **kwargs):
+        """Front half of ``EventChatModel.generate`` (model/EventChatModel.py:246-292): same argument handling and the same
+        two ``NotImplementedError``s; everything up to the hand-over to the language model.  This front end does not own
+        the LLM, so the embedding table is passed in and the call returns the keyword arguments upstream forwards to
+        ``super().generate`` (``position_ids``, ``attention_mask``, ``inputs_embeds`` + the caller's own); with ``llm`` given
+        it forwards them to ``llm.generate`` instead.  ``event_image_sizes`` is accepted and never read, as upstream."""
+        position_ids = kwargs.pop("position_ids", None)
+        attention_mask = kwargs.pop("attention_mask", None)
+        if "inputs_embeds" in kwargs:
+            raise NotImplementedError("`inputs_embeds` is not supported")
+        if event_tensors is None and event_features is None:
+            raise NotImplementedError("please input Event")
+        _, position_ids, attention_mask, _, inputs_embeds, _ = self.prepare_inputs_labels_for_multimodal(
+            embed_table, inputs, position_ids, attention_mask, None, None, event_tensors=event_tensors,
+            event_image_sizes=event_image_sizes, event_features=event_features)
+        out = dict(position_ids=position_ids, attention_mask=attention_mask, inputs_embeds=inputs_embeds, **kwargs)
+        return llm.generate(**out) if llm is not None else out
+
     # ---- fused path: events -> tokens ------------------------------------------------------------
     def visual_tokens(self, x, y, p, window_offsets, sensor_size, n_frames=E.N_FRAMES, out=None, check_flags=True):
         """process_event_data (common/common.py:110-129) + the list branch (:326-343) for a batch of

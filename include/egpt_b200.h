@@ -196,8 +196,9 @@ int egpt_spatio_temporal_pool(const void* features, int is_f32, int batch, int t
 
 /* a-9  list branch of prepare_inputs_labels_for_multimodal      model/EventChatModel.py:326-343 */
 /* pixel_values bf16 [B*n,3,336,336] -> tokens bf16 [B, n+577, 4096]: tower, projector, adaptor, */
-/* pooling.  The adaptor is applied after the pooling (it is affine, so the result is the same   */
-/* up to rounding).                                                                */
+/* pooling.  The pooling is a mean and the projector's second linear and the adaptor are affine, */
+/* so both run AFTER the pooling, on n+577 instead of n*577 rows per window (the result is the   */
+/* same up to rounding).                                                           */
 int egpt_encode_pool(egpt_handle* h, const uint16_t* pixel_values, int n_windows, int n_frames,
                      uint16_t* out_tokens, void* workspace, size_t workspace_bytes, void* stream);
 

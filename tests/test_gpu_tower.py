@@ -318,3 +318,31 @@ def test_attention_lazy_rescale_and_peaked_rows(dev):
     err = (out.float() - ref).abs().max().item()
     assert torch.isfinite(out.float()).all() and err < 3e-2, err
     assert _cos(out.float(), ref) > 0.9999
+
+
+def test_generate_front_half(frontends, dev):
+    """model/EventChatModel.py:246-292 up to the hand-over to the language model: the two NotImplementedErrors, the cached
+    `event_features` branch (adaptor re-applied, as upstream) and the tensors that upstream forwards to `super().generate`."""
+    from eventgpt_b200.model import splice_event_features
+    sd, fe = frontends(2)
+    g = torch.Generator(device="cpu").manual_seed(9)
+    table = (torch.randn(320, 4096, generator=g) * 0.02).bfloat16().to(dev)
+    ids = torch.randint(0, 300, (2, 12), generator=g)
+    ids[0, 3] = -200
+    ids[1, 7] = -200                                         # EVENT_TOKEN_INDEX
+    ids = ids.to(dev)
+    with pytest.raises(NotImplementedError, match="please input Event"):
+        fe.generate(table, ids)
+    with pytest.raises(NotImplementedError, match="inputs_embeds"):
+        fe.generate(table, ids, event_features=torch.zeros(2, 582, 4096), inputs_embeds=torch.zeros(1))
+    feats = (torch.randn(2, 582, 4096, generator=g) * 0.1).bfloat16().to(dev)
+    out = fe.generate(table, ids, event_features=feats, max_new_tokens=7)
+    assert out["max_new_tokens"] == 7 and out["position_ids"] is None and out["attention_mask"] is None
+    want = splice_event_features(table, ids, None, None, None, fe.feature_adaptor(feats))[2]
+    assert tuple(out["inputs_embeds"].shape) == (2, 11 + 582, 4096) and torch.equal(out["inputs_embeds"], want)
+
+    class FakeLLM:                                           # the hand-over itself
+        def generate(self, **kw):
+            return sorted(kw)
+    assert fe.generate(table, ids, event_features=feats, llm=FakeLLM(), do_sample=False) == [
+        "attention_mask", "do_sample", "inputs_embeds", "position_ids"]
