@@ -122,6 +122,16 @@ im2col_kernel(const uint16_t* __restrict__ pix, uint16_t* __restrict__ patches, 
 // sum per frame into `partial` [B, chunks, t, c] fp32; pool_finish sums the chunks in order.
 template <typename T> struct Vec8;
 template <> struct Vec8<__nv_bfloat16> {
+  typedef uint4 Raw;                                    // 8 values as loaded (kept packed while in flight)
+  static __device__ __forceinline__ Raw load_raw(const __nv_bfloat16* p) { return *reinterpret_cast<const uint4*>(p); }
+  static __device__ __forceinline__ void unpack(const Raw& u, float (&v)[8]) {
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = __uint_as_float(w[i] << 16);
+      v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
   static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&v)[8]) {
     const uint4 u = *reinterpret_cast<const uint4*>(p);
     const uint32_t w[4] = {u.x, u.y, u.z, u.w};
@@ -137,6 +147,13 @@ template <> struct Vec8<__nv_bfloat16> {
   }
 };
 template <> struct Vec8<float> {
+  struct Raw { float4 a, b; };
+  static __device__ __forceinline__ Raw load_raw(const float* p) {
+    return Raw{reinterpret_cast<const float4*>(p)[0], reinterpret_cast<const float4*>(p)[1]};
+  }
+  static __device__ __forceinline__ void unpack(const Raw& r, float (&v)[8]) {
+    v[0] = r.a.x; v[1] = r.a.y; v[2] = r.a.z; v[3] = r.a.w; v[4] = r.b.x; v[5] = r.b.y; v[6] = r.b.z; v[7] = r.b.w;
+  }
   static __device__ __forceinline__ void load(const float* p, float (&v)[8]) {
     const float4 a = reinterpret_cast<const float4*>(p)[0], b = reinterpret_cast<const float4*>(p)[1];
     v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
@@ -150,7 +167,7 @@ template <> struct Vec8<float> {
 constexpr int kPoolMaxT = 8;
 constexpr int kPoolRows = 32;     // spatial positions per CTA
 
-template <typename T>
+template <typename T, int TMAX>
 __global__ void __launch_bounds__(128)
 pool_kernel(const T* __restrict__ feat, int t, int s, int c, int n_temporal, T* __restrict__ out,
             float* __restrict__ partial) {
@@ -158,29 +175,45 @@ pool_kernel(const T* __restrict__ feat, int t, int s, int c, int n_temporal, T* 
   const int col = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
   if (col >= c) return;
   const int s0 = chunk * kPoolRows, s1 = min(s, s0 + kPoolRows);
-  float tacc[kPoolMaxT][8];
+  float tacc[TMAX][8];
 #pragma unroll
-  for (int i = 0; i < kPoolMaxT; ++i)
+  for (int i = 0; i < TMAX; ++i)
 #pragma unroll
     for (int j = 0; j < 8; ++j) tacc[i][j] = 0.f;
   const float inv_t = 1.0f / (float)t;
-  for (int si = s0; si < s1; ++si) {
-    float sp[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  // two spatial positions per iteration: 2 t independent 16-byte loads in flight per thread, kept packed until used
+  // (the kernel is a pure stream; the additions happen in the same order as a one-row-at-a-time loop)
+  for (int si = s0; si < s1; si += 2) {
+    const bool two = si + 1 < s1;
+    typename Vec8<T>::Raw raw[2][TMAX];
 #pragma unroll
-    for (int ti = 0; ti < kPoolMaxT; ++ti) {
+    for (int ti = 0; ti < TMAX; ++ti) {
       if (ti < t) {
-        float v[8];
-        Vec8<T>::load(feat + (((size_t)b * t + ti) * s + si) * c + col, v);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { sp[j] += v[j]; tacc[ti][j] += v[j]; }
+        const T* src = feat + (((size_t)b * t + ti) * s + si) * c + col;
+        raw[0][ti] = Vec8<T>::load_raw(src);
+        if (two) raw[1][ti] = Vec8<T>::load_raw(src + c);
       }
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) sp[j] *= inv_t;
-    Vec8<T>::store(out + ((size_t)b * (n_temporal + s) + n_temporal + si) * c + col, sp);
+    for (int r = 0; r < 2; ++r) {
+      if (r == 1 && !two) break;
+      float sp[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+      for (int ti = 0; ti < TMAX; ++ti) {
+        if (ti < t) {
+          float v[8];
+          Vec8<T>::unpack(raw[r][ti], v);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) { sp[j] += v[j]; tacc[ti][j] += v[j]; }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sp[j] *= inv_t;
+      Vec8<T>::store(out + ((size_t)b * (n_temporal + s) + n_temporal + si + r) * c + col, sp);
+    }
   }
 #pragma unroll
-  for (int ti = 0; ti < kPoolMaxT; ++ti)
+  for (int ti = 0; ti < TMAX; ++ti)
     if (ti < t) {
       float* p = partial + (((size_t)b * chunks + chunk) * t + ti) * c + col;
       reinterpret_cast<float4*>(p)[0] = make_float4(tacc[ti][0], tacc[ti][1], tacc[ti][2], tacc[ti][3]);
@@ -335,14 +368,16 @@ extern "C" int egpt_spatio_temporal_pool(const void* features, int is_f32, int b
   dim3 grid((c / 8 + 127) / 128, chunks, batch);
   const long long total = (long long)batch * n_temporal * c;
   if (is_f32) {
-    pool_kernel<float><<<grid, 128, 0, st>>>((const float*)features, t, s, c, n_temporal, (float*)out, partial);
+    if (t <= 5) pool_kernel<float, 5><<<grid, 128, 0, st>>>((const float*)features, t, s, c, n_temporal, (float*)out, partial);
+    else pool_kernel<float, kPoolMaxT><<<grid, 128, 0, st>>>((const float*)features, t, s, c, n_temporal, (float*)out, partial);
     EGPT_LAUNCH_CHECK();
     if (total > 0) {
       pool_finish_kernel<float><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(partial, chunks, t, s, c, n_temporal, (float*)out, total);
       EGPT_LAUNCH_CHECK();
     }
   } else {
-    pool_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>((const __nv_bfloat16*)features, t, s, c, n_temporal, (__nv_bfloat16*)out, partial);
+    if (t <= 5) pool_kernel<__nv_bfloat16, 5><<<grid, 128, 0, st>>>((const __nv_bfloat16*)features, t, s, c, n_temporal, (__nv_bfloat16*)out, partial);
+    else pool_kernel<__nv_bfloat16, kPoolMaxT><<<grid, 128, 0, st>>>((const __nv_bfloat16*)features, t, s, c, n_temporal, (__nv_bfloat16*)out, partial);
     EGPT_LAUNCH_CHECK();
     if (total > 0) {
       pool_finish_kernel<__nv_bfloat16><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(partial, chunks, t, s, c, n_temporal, (__nv_bfloat16*)out, total);
