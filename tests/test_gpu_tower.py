@@ -346,3 +346,19 @@ def test_generate_front_half(frontends, dev):
             return sorted(kw)
     assert fe.generate(table, ids, event_features=feats, llm=FakeLLM(), do_sample=False) == [
         "attention_mask", "do_sample", "inputs_embeds", "position_ids"]
+
+
+def test_fused_op_order_matches_reference_order(frontends, sample_frames, dev):
+    """The fused token path pools the projector's GELU output BEFORE the projector's second linear and the adaptor (both affine,
+    the pooling a mean).  Cross-check against the reference's own order built from the unfused entry points: visval_encode per
+    frame -> feature_adaptor per token -> get_spatio_temporal_features (model/EventChatModel.py:333-341).  Same function, one
+    rounding point moved: the two must agree to bf16 rounding noise."""
+    from eventgpt_b200.model import get_spatio_temporal_features
+    sd, fe = frontends(2)
+    fused = fe.encode_events(sample_frames)[0].float()
+    per_frame = [fe.feature_adaptor(fe.visval_encode(f[None]))[0] for f in sample_frames]     # reference order, per token
+    ref_order = get_spatio_temporal_features(per_frame).float()
+    assert tuple(fused.shape) == tuple(ref_order.shape) == (582, 4096)
+    d = (fused - ref_order).abs()
+    scale = ref_order.abs().max().item()
+    assert d.max().item() < 2e-2 * max(scale, 1.0) and _cos(fused, ref_order) > 0.9999, (d.max().item(), scale)
