@@ -18,7 +18,8 @@ namespace egpt {
 constexpr int kCrop = EGPT_CROP;
 constexpr int kTaps = EGPT_MAX_TAPS;
 constexpr int kPrecisionBits = 32 - 8 - 2;
-constexpr int kAxisInts = kCrop * (2 + kTaps);        // xmin[336], cnt[336], k[336][taps]
+constexpr int kAxisInts = kCrop * (2 + kTaps);        // xmin[336], cnt[336], then the taps: horizontal axis k[taps][336] (lanes of a warp
+                                                      // = neighbouring output columns read neighbouring words), vertical axis k[336][taps]
 constexpr int kPatchK = 640;                           // 3*14*14 = 588 padded to a multiple of 64
 
 struct Geometry { int new_h, new_w, top, left; };
@@ -90,7 +91,7 @@ resize_coeffs_kernel(const int32_t* __restrict__ hw, int32_t* __restrict__ table
     double v = wts[x];
     if (ww != 0.0) v = __ddiv_rn(v, ww);
     const double s = __dmul_rn(v, (double)(1 << kPrecisionBits));
-    tab[2 * kCrop + o * kTaps + x] = v < 0 ? (int)__dadd_rn(-0.5, s) : (int)__dadd_rn(0.5, s);
+    tab[2 * kCrop + (axis == 0 ? x * kCrop + o : o * kTaps + x)] = v < 0 ? (int)__dadd_rn(-0.5, s) : (int)__dadd_rn(0.5, s);
   }
   tab[o] = xmin;
   tab[kCrop + o] = cnt;
@@ -130,10 +131,10 @@ resample_horizontal_kernel(const uint8_t* __restrict__ frames, size_t frame_stri
   if (o >= kCrop) return;
   const int32_t* tab = tables + ((size_t)f * 2 + 0) * kAxisInts;
   const int xmin = tab[o], cnt = tab[kCrop + o];
-  const int32_t* k = tab + 2 * kCrop + o * kTaps;
+  const int32_t* k = tab + 2 * kCrop + o;                   // tap j of this column at k[j * kCrop]
   int kr[12];
 #pragma unroll
-  for (int j = 0; j < 12; ++j) kr[j] = j < cnt ? __ldg(k + j) : 0;
+  for (int j = 0; j < 12; ++j) kr[j] = j < cnt ? __ldg(k + j * kCrop) : 0;
   uint8_t* dst = tmp + (size_t)f * tmp_stride;
   for (int y = y0; y < y1; ++y) {
     const size_t gs = (size_t)y * w * 3;
@@ -145,7 +146,7 @@ resample_horizontal_kernel(const uint8_t* __restrict__ frames, size_t frame_stri
         if (j < cnt) { a0 += row[3 * j + 0] * kr[j]; a1 += row[3 * j + 1] * kr[j]; a2 += row[3 * j + 2] * kr[j]; }
     } else {
       for (int j = 0; j < cnt; ++j) {
-        const int kj = __ldg(k + j);
+        const int kj = __ldg(k + j * kCrop);
         a0 += row[3 * j + 0] * kj; a1 += row[3 * j + 1] * kj; a2 += row[3 * j + 2] * kj;
       }
     }
