@@ -362,3 +362,43 @@ def test_fused_op_order_matches_reference_order(frontends, sample_frames, dev):
     d = (fused - ref_order).abs()
     scale = ref_order.abs().max().item()
     assert d.max().item() < 2e-2 * max(scale, 1.0) and _cos(fused, ref_order) > 0.9999, (d.max().item(), scale)
+
+
+def test_config5_events_to_inputs_embeds(frontends, dev):
+    """BASELINE configs[4] shape at test scale: raw events of several ragged windows (one of 2 M events, as configs[2]) ->
+    visual tokens -> multimodal splice -> `inputs_embeds`, all on the device.  The tokens of every window equal that window
+    processed alone; the splice is bit-exact against the oracle splice fed with those tokens; prompt rows are untouched."""
+    from eventgpt_b200 import events as E
+    from oracle import splice as osp
+    sd, fe = frontends(2)
+    rng = np.random.default_rng(55)
+    H, W = 480, 640
+    sizes = [2_000_000, 300_000, 1_000_000]
+    n = sum(sizes)
+    x = torch.from_numpy(rng.integers(0, W, n).astype(np.uint16)).to(dev)
+    y = torch.from_numpy(rng.integers(0, H, n).astype(np.uint16)).to(dev)
+    p = torch.from_numpy(rng.integers(0, 2, n).astype(np.uint8)).to(dev)
+    off = torch.tensor(np.concatenate([[0], np.cumsum(sizes)]), dtype=torch.int64, device=dev)
+    tok = fe.visual_tokens(x, y, p, off, (H, W))
+    assert tuple(tok.shape) == (3, 582, 4096) and torch.isfinite(tok.float()).all()
+    s, e = int(off[1]), int(off[2])
+    alone = fe.visual_tokens(x[s:e].clone(), y[s:e].clone(), p[s:e].clone(), torch.tensor([0, e - s], dtype=torch.int64, device=dev), (H, W))
+    assert torch.equal(alone[0], tok[1])
+    # prompts: one <event> each, different lengths, right padding via the attention mask
+    g = torch.Generator(device="cpu").manual_seed(7)
+    table = (torch.randn(512, 4096, generator=g) * 0.02).bfloat16()
+    L = 40
+    ids = torch.randint(0, 500, (3, L), generator=g)
+    mask = torch.ones(3, L, dtype=torch.bool)
+    for b, (pos, length) in enumerate([(5, 40), (0, 23), (30, 31)]):
+        ids[b, pos] = -200
+        mask[b, length:] = False
+    out = fe.prepare_inputs_labels_for_multimodal(table.to(dev), ids.to(dev), None, mask.to(dev), None, None, event_features=None,
+                                                  event_tensors=None)
+    assert out[4] is None                                            # no events given: untouched, as upstream
+    from eventgpt_b200.model import splice_event_features
+    pos_ids, am, emb, lab = splice_event_features(table.to(dev), ids.to(dev), None, mask.to(dev), None, tok)
+    want = osp.splice(table.float(), ids, None, mask, None, tok.float().cpu())
+    assert tuple(emb.shape) == tuple(want[2].shape) == (3, 39 + 582, 4096)
+    assert torch.equal(emb.float().cpu(), want[2]) and torch.equal(am.cpu(), want[1])
+    assert torch.equal(emb[0, :5].cpu(), table[ids[0, :5]]) and torch.equal(emb[0, 5:5 + 582], tok[0])
