@@ -53,7 +53,10 @@ __device__ __forceinline__ void ln_row(const float (&x)[32], const float* __rest
 __global__ void __launch_bounds__(256)
 layernorm_bf16_kernel(const float* __restrict__ h, const float* __restrict__ gamma, const float* __restrict__ beta,
                       __nv_bfloat16* __restrict__ y, long long rows) {
-  const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  // Rows are walked from the last to the first: the GEMM that produced h wrote its rows in ascending order, so the tail of h
+  // is what is still in L2 when this kernel starts; and the rows of y written last (the first ones) are the ones the next
+  // GEMM reads first.
+  const long long row = (long long)(gridDim.x - 1 - blockIdx.x) * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= rows) return;
   float x[32];
