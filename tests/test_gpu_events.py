@@ -262,3 +262,26 @@ def test_overlap_clips_rasterise_like_reference(dev):
         want = oev.get_event_images_list(sub, 5)
         for i in range(5):
             assert np.array_equal(got[b * 5 + i], want[i]), (b, i)
+
+
+@pytest.mark.parametrize("h,w", [(1100, 2000), (340, 1900), (1500, 400)])
+def test_preprocess_arbitrary_images_wide_and_deep_filters(h, w, dev):
+    """egpt_preprocess on arbitrary uint8 images (the PNG path) at sizes that leave the common fast paths:
+    (1100, 2000): rows too wide for the shared-memory staging AND more than 12 filter taps on both axes (scale 3.3);
+    (340, 1900): almost no vertical scaling but a 5.6x horizontal reduction (23 taps); (1500, 400): tall, horizontal up-scale.
+    Bit-exact against the CPU restatement of Pillow's fixed-point bicubic + the CLIP normalisation."""
+    from eventgpt_b200 import events as E
+    from oracle import preprocess as opp
+    rng = np.random.default_rng(h * 10007 + w)
+    img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    img[::7, ::5] = 255
+    img[3::11, 2::3] = 0
+    stride = (h * w * 3 + 255) // 256 * 256
+    frames = torch.zeros((1, stride), dtype=torch.uint8, device=dev)
+    frames[0, :h * w * 3] = torch.from_numpy(img.reshape(-1)).to(dev)
+    hw = torch.tensor([[h, w]], dtype=torch.int32, device=dev)
+    px, _, st = E.preprocess(frames, hw, h)
+    E.check_status(st, "preprocess")
+    got = px.view(torch.int16).cpu().numpy().view(np.uint16)[0]
+    want = opp.pixel_values_bf16_bits(img)
+    assert np.array_equal(got, want)
