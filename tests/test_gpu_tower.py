@@ -402,3 +402,26 @@ def test_config5_events_to_inputs_embeds(frontends, dev):
     assert tuple(emb.shape) == tuple(want[2].shape) == (3, 39 + 582, 4096)
     assert torch.equal(emb.float().cpu(), want[2]) and torch.equal(am.cpu(), want[1])
     assert torch.equal(emb[0, :5].cpu(), table[ids[0, :5]]) and torch.equal(emb[0, 5:5 + 582], tok[0])
+
+
+@pytest.mark.parametrize("n", [1, 3, 8])
+def test_other_frame_counts(n, frontends, dev):
+    """get_event_images_list(event_npy, n) takes any n (common/common.py:17-37; the inference caller passes 5): raster,
+    preprocessing and the fused token path for 1, 3 and 8 frames per window -> tokens [B, n + 577, 4096]."""
+    from eventgpt_b200 import events as E
+    from oracle import events as oev, preprocess as opp
+    sd, fe = frontends(2)
+    ev, _, _ = load_golden_events("dsec_000099")
+    H, W = 480, 640
+    x, y, p = (E.to_device(ev[k].astype(np.uint16 if k != "p" else np.uint8), dev) for k in "xyp")
+    off = torch.tensor([0, len(ev["t"])], dtype=torch.int64, device=dev)
+    fr, hw, _, st = E.raster(x, y, p, off, 1, n, H, W)
+    E.check_status(st, "raster")
+    want_frames = oev.get_event_images_list(ev, n)
+    got_frames = E.frames_to_numpy(fr, hw)
+    assert len(got_frames) == n and all(np.array_equal(a, b) for a, b in zip(got_frames, want_frames))
+    tok = fe.visual_tokens(x, y, p, off, (H, W), n_frames=n)
+    assert tuple(tok.shape) == (1, n + 577, 4096)
+    pix = [torch.from_numpy(opp.bf16_bits_to_f32(opp.pixel_values_bf16_bits(f))).to(dev).bfloat16() for f in want_frames]
+    want = fe.encode_events(pix)
+    assert torch.equal(tok[0], want[0])
