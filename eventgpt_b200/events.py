@@ -35,13 +35,16 @@ def ptr(t):
 
 
 class Workspace:
-    """Grow-only device scratch buffers, one set per (device, tag).  The library itself never
-    allocates on the data path; this is the caller-side allocation it asks for."""
+    """Grow-only device scratch buffers, one set per (device, current CUDA stream, tag).  The library itself never
+    allocates on the data path; this is the caller-side allocation it asks for.  The C ABI is re-entrant per
+    (handle, stream, workspace) -- the reference's e2e benchmark runs prefills from two Python threads on two
+    streams (pipeline/benchmark_e2e/benchmark_e2e_wallclock.py:641-649) -- so scratch is never shared between streams."""
     _bufs = {}
 
     @classmethod
     def get(cls, device, tag, nbytes):
-        key = (torch.device(device).index or 0, tag)
+        dev = torch.device(device)
+        key = (dev.index or 0, int(torch.cuda.current_stream(dev).cuda_stream), tag)
         buf = cls._bufs.get(key)
         if buf is None or buf.numel() < nbytes:
             buf = None

@@ -425,3 +425,43 @@ def test_other_frame_counts(n, frontends, dev):
     pix = [torch.from_numpy(opp.bf16_bits_to_f32(opp.pixel_values_bf16_bits(f))).to(dev).bfloat16() for f in want_frames]
     want = fe.encode_events(pix)
     assert torch.equal(tok[0], want[0])
+
+
+def test_two_threads_two_streams(frontends, dev):
+    """Re-entrancy per (handle, stream, workspace): two Python threads drive the same front end on two CUDA streams at once
+    (the reference's e2e benchmark does this with its two prefills, pipeline/benchmark_e2e/benchmark_e2e_wallclock.py:641-649).
+    Each thread's tokens equal the ones computed alone."""
+    import threading
+    from eventgpt_b200 import events as E
+    sd, fe = frontends(2)
+    rng = np.random.default_rng(77)
+    H, W, N = 480, 640, 400_000
+    data = []
+    for k in range(2):
+        x = torch.from_numpy(rng.integers(0, W, N).astype(np.uint16)).to(dev)
+        y = torch.from_numpy(rng.integers(0, H, N).astype(np.uint16)).to(dev)
+        p = torch.from_numpy(rng.integers(0, 2, N).astype(np.uint8)).to(dev)
+        off = torch.tensor([0, N // 2, N], dtype=torch.int64, device=dev)
+        data.append((x, y, p, off))
+    alone = [fe.visual_tokens(*d, (H, W)).clone() for d in data]
+    torch.cuda.synchronize(dev)
+    out, errs = [None, None], []
+
+    def work(k):
+        try:
+            s = torch.cuda.Stream(dev)
+            with torch.cuda.stream(s):
+                for _ in range(3):
+                    out[k] = fe.visual_tokens(*data[k], (H, W))
+            s.synchronize()
+        except Exception as e:      # pragma: no cover
+            errs.append(e)
+
+    ts = [threading.Thread(target=work, args=(k,)) for k in range(2)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errs, errs
+    for k in range(2):
+        assert torch.equal(out[k], alone[k]), k
