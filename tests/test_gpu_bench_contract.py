@@ -1,0 +1,35 @@
+"""bench.py's one-line JSON contract, checked on the GPU (the CPU side is covered by tests/test_host_logic_cpu.py)."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pytestmark = pytest.mark.gpu
+
+
+def test_bench_line_has_every_contract_key():
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "2", "--warmup", "3", "--no-cpu-baseline"],
+                         capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.strip().splitlines() if l.startswith("{")]
+    assert len(lines) == 1                                   # exactly ONE JSON line
+    j = json.loads(lines[0])
+    for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline",
+              "dtype", "data", "config", "e2e", "gpu_launches", "clocks", "roofline"):
+        assert k in j, k
+    assert j["metric"] == "event_windows_per_s_to_visual_tokens" and j["unit"] == "windows/s" and j["n_gpus"] == 1
+    assert j["steps"] == 2 and j["warmup"] == 3 and j["higher_is_better"] is True and j["scaling"] == "weak" and j["vs_baseline"] is None
+    assert "workload" in j["config"] and "model" not in j["config"]
+    assert abs(j["value"] - 32 / (j["ms_per_step"] * 1e-3)) < 1e-6 * j["value"]
+    assert j["gpu_launches"] > 100
+    e = j["e2e"]
+    assert e["value"] > 0 and e["h2d_bytes_per_step"] == 32 * 1_000_000 * 5 + 33 * 8 and e["d2h_bytes_per_step"] == 32 * 582 * 4096 * 2
+    r = j["roofline"]
+    for k in ("bound", "achieved", "peak", "unit", "frac", "traffic"):
+        assert k in r, k
+    assert r["bound"] == "tensor" and r["unit"] == "TFLOP/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9 and 0.3 < r["frac"] < 1.2
+    c = j["clocks"]
+    assert c["sm_mhz"] and c["sm_max_mhz"] and isinstance(c["reasons"], list)
