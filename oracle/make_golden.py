@@ -243,9 +243,63 @@ def splice_inputs():
     return table, feats
 
 
+def clips_inputs():
+    """Seeded recording for the 50 %-overlap clip splitter: sorted t with an 80 ms hole, shuffled image timestamps."""
+    rng = np.random.default_rng(31)
+    t = np.sort(rng.integers(1_000_000, 1_600_000, 20_000)).astype(np.int64)
+    t = t[(t < 1_200_000) | (t >= 1_280_000)]
+    n = len(t)
+    ev = {"x": rng.integers(0, 640, n).astype(np.uint16), "y": rng.integers(0, 480, n).astype(np.uint16),
+          "p": rng.integers(0, 2, n).astype(np.uint8), "t": t}
+    stamps = [1_000_000 + 50_000 * i for i in range(12)]
+    stamps[3], stamps[7] = stamps[7], stamps[3]
+    return ev, stamps
+
+
+def make_clips_golden():
+    """split_event_by_time of the DSEC clip builder (feasible/my_egpt_dsec_dataset/build_my_egpt_dsec_seq.py:137-225) through
+    the REAL reference function.  The module imports h5py (absent here, unused by this function) at its top, so a stub module
+    stands in for it during the import -- the same trick as the peft stub of ref_harness."""
+    import contextlib, importlib.util, io, types
+    had = "h5py" in sys.modules
+    if not had:
+        sys.modules["h5py"] = types.ModuleType("h5py")
+    try:
+        spec = importlib.util.spec_from_file_location(
+            "ref_build_seq", os.path.join(REF, "feasible", "my_egpt_dsec_dataset", "build_my_egpt_dsec_seq.py"))
+        mod = importlib.util.module_from_spec(spec)
+        with contextlib.redirect_stdout(io.StringIO()):
+            spec.loader.exec_module(mod)
+    finally:
+        if not had:
+            del sys.modules["h5py"]
+    ev, stamps = clips_inputs()
+    out = {}
+    for name, interval, st in (("a", 50_000, stamps), ("b", 33_333, stamps), ("fallback", 50_000, None)):
+        with contextlib.redirect_stdout(io.StringIO()):
+            clips = mod.split_event_by_time(ev, time_interval=interval, image_timestamps=st)
+        out[f"{name}_n"] = np.int64(len(clips))
+        out[f"{name}_time_start"] = np.array([c["time_start"] for c in clips], dtype=np.int64)
+        out[f"{name}_time_end"] = np.array([c["time_end"] for c in clips], dtype=np.int64)
+        if "indices" in clips[0]:
+            out[f"{name}_first"] = np.array([c["indices"][0] for c in clips], dtype=np.int64)
+            out[f"{name}_count"] = np.array([c["num_events"] for c in clips], dtype=np.int64)
+            out[f"{name}_index_sum"] = np.array([int(c["indices"].sum()) for c in clips], dtype=np.int64)
+            out[f"{name}_image_idx"] = np.array([c["image_idx"] for c in clips], dtype=np.int64)
+            out[f"{name}_n_images"] = np.array([len(c["image_indices_in_clip"]) for c in clips], dtype=np.int64)
+        else:
+            out[f"{name}_count"] = np.array([len(c["t"]) for c in clips], dtype=np.int64)
+            out[f"{name}_xsum"] = np.array([int(c["x"].astype(np.int64).sum()) for c in clips], dtype=np.int64)
+    np.savez_compressed(os.path.join(OUT, "clips.npz"), **out)
+    print("clips.npz:", {k: (v.shape if hasattr(v, "shape") else v) for k, v in out.items() if k.endswith("_n")})
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "splice":
         make_splice_golden()
+    elif len(sys.argv) > 1 and sys.argv[1] == "clips":
+        make_clips_golden()
     else:
         main()
         make_splice_golden()
+        make_clips_golden()

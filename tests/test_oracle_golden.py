@@ -118,3 +118,28 @@ def test_splice_matches_reference():
     pos2, am2, emb2, lab2 = osp.splice(table, ids, pid, None, None, feats)
     assert am2 is None and lab2 is None and np.array_equal(pos2.numpy(), z["pos2"])
     assert np.allclose(emb2.double().sum(-1).numpy(), z["emb2_rowsum"])
+
+
+@pytest.mark.parametrize("name,interval,with_stamps", [("a", 50_000, True), ("b", 33_333, True), ("fallback", 50_000, False)])
+def test_clip_splitter_vs_reference_golden(name, interval, with_stamps):
+    """oracle.events.split_event_by_time_clips and the product's io.split_event_by_time_clips against the REAL
+    build_my_egpt_dsec_seq.split_event_by_time (tests/golden/clips.npz, oracle/make_golden.py clips)."""
+    from oracle import events as oev
+    from oracle.make_golden import clips_inputs
+    from eventgpt_b200 import io as eio
+    z = np.load(os.path.join(GOLDEN, "clips.npz"))
+    ev, stamps = clips_inputs()
+    for impl in (oev.split_event_by_time_clips, eio.split_event_by_time_clips):
+        clips = impl(ev, interval, stamps if with_stamps else None)
+        assert len(clips) == int(z[f"{name}_n"]) and len(clips) > 5
+        assert [int(c["time_start"]) for c in clips] == z[f"{name}_time_start"].tolist()
+        assert [int(c["time_end"]) for c in clips] == z[f"{name}_time_end"].tolist()
+        if with_stamps:
+            assert [int(c["indices"][0]) for c in clips] == z[f"{name}_first"].tolist()
+            assert [int(c["num_events"]) for c in clips] == z[f"{name}_count"].tolist()
+            assert [int(np.asarray(c["indices"]).sum()) for c in clips] == z[f"{name}_index_sum"].tolist()
+            assert [int(c["image_idx"]) for c in clips] == z[f"{name}_image_idx"].tolist()
+            assert [len(c["image_indices_in_clip"]) for c in clips] == z[f"{name}_n_images"].tolist()
+        else:
+            assert [len(c["t"]) for c in clips] == z[f"{name}_count"].tolist()
+            assert [int(c["x"].astype(np.int64).sum()) for c in clips] == z[f"{name}_xsum"].tolist()
