@@ -294,8 +294,66 @@ def make_clips_golden():
     print("clips.npz:", {k: (v.shape if hasattr(v, "shape") else v) for k, v in out.items() if k.endswith("_n")})
 
 
+def io_recording(seed=0, n=200_000, dur_ms=400):
+    """Seeded in-memory recording in the DSEC layout (events/{x,y,p,t}, ms_to_idx, t_offset)."""
+    rng = np.random.default_rng(seed)
+    t = np.sort(rng.integers(0, dur_ms * 1000, n)).astype(np.uint32)
+    ms_to_idx = np.searchsorted(t, np.arange(dur_ms + 1) * 1000, side="left").astype(np.uint64)
+    return {"events": {"x": rng.integers(0, 640, n).astype(np.uint16), "y": rng.integers(0, 480, n).astype(np.uint16),
+                       "p": rng.integers(0, 2, n).astype(np.uint8), "t": t},
+            "ms_to_idx": ms_to_idx, "t_offset": np.array(51_000_000_000, dtype=np.int64)}
+
+
+IO_WINDOWS = [(51_000_050_000, 51_000_100_000), (51_000_000_000, 51_000_050_000), (51_000_123_456, 51_000_301_999),
+              (51_000_399_000, 51_000_399_500)]
+IO_RANGES = [(0, 10), (1234, 98_765), (199_990, 200_000)]
+
+
+def make_io_golden():
+    """dataset/io.py:38-87 through the REAL reference functions.  h5py is absent from the image; the reference only uses
+    `h5py.File(path, 'r')` as a context manager and indexes the handle, so a stub module whose File returns the in-memory
+    recording stands in for it."""
+    import importlib.util, types
+
+    class FakeFile:
+        def __init__(self, rec): self.rec = rec
+        def __enter__(self): return self
+        def __exit__(self, *a): return False
+        def __getitem__(self, key):
+            node = self.rec
+            for part in key.split("/"):
+                node = node[part]
+            return node
+
+    rec = io_recording()
+    stub = types.ModuleType("h5py")
+    stub.File = lambda path, mode="r": FakeFile(rec)
+    had = sys.modules.get("h5py")
+    sys.modules["h5py"] = stub
+    try:
+        spec = importlib.util.spec_from_file_location("ref_dataset_io", os.path.join(REF, "dataset", "io.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+    finally:
+        if had is None:
+            del sys.modules["h5py"]
+        else:
+            sys.modules["h5py"] = had
+    out = {"num_events": np.int64(mod.get_num_events("recording.h5"))}
+    def summary(d):
+        return np.array([len(d["t"]), int(d["t"][0]) if len(d["t"]) else -1, int(d["t"][-1]) if len(d["t"]) else -1,
+                         int(d["x"].astype(np.int64).sum()), int(d["y"].astype(np.int64).sum()), int(d["p"].astype(np.int64).sum()),
+                         int(d["t"].dtype == np.int64)], dtype=np.int64)
+    out["windows"] = np.stack([summary(mod.extract_from_h5_by_timewindow("recording.h5", a, b)) for a, b in IO_WINDOWS])
+    out["ranges"] = np.stack([summary(mod.extract_from_h5_by_index("recording.h5", a, b)) for a, b in IO_RANGES])
+    np.savez_compressed(os.path.join(OUT, "dsec_io.npz"), **out)
+    print("dsec_io.npz:", out["windows"][:, 0].tolist(), out["ranges"][:, 0].tolist())
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "splice":
+    if len(sys.argv) > 1 and sys.argv[1] == "io":
+        make_io_golden()
+    elif len(sys.argv) > 1 and sys.argv[1] == "splice":
         make_splice_golden()
     elif len(sys.argv) > 1 and sys.argv[1] == "clips":
         make_clips_golden()
@@ -303,3 +361,4 @@ if __name__ == "__main__":
         main()
         make_splice_golden()
         make_clips_golden()
+        make_io_golden()

@@ -103,3 +103,22 @@ def test_overlap_clips_fallbacks():
             assert g["time_start"] == w["time_start"] and g["time_end"] == w["time_end"] and g["duration_ms"] == w["duration_ms"]
             for k in "xytp":
                 np.testing.assert_array_equal(g[k], w[k])
+
+
+def test_dsec_io_mirrors_vs_reference_golden():
+    """eventgpt_b200.io against the REAL dataset/io.py functions (tests/golden/dsec_io.npz, produced by
+    `python -m oracle.make_golden io`, where a stub h5py hands the reference an in-memory recording)."""
+    import os
+    from oracle.make_golden import IO_RANGES, IO_WINDOWS, io_recording
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "dsec_io.npz"))
+    rec = io_recording()
+
+    def summary(d):
+        return [len(d["t"]), int(d["t"][0]) if len(d["t"]) else -1, int(d["t"][-1]) if len(d["t"]) else -1,
+                int(d["x"].astype(np.int64).sum()), int(d["y"].astype(np.int64).sum()), int(d["p"].astype(np.int64).sum()),
+                int(d["t"].dtype == np.int64)]
+    assert eio.get_num_events(rec) == int(z["num_events"])
+    for (a, b), want in zip(IO_WINDOWS, z["windows"].tolist()):
+        assert summary(eio.extract_from_h5_by_timewindow(rec, a, b)) == want
+    for (a, b), want in zip(IO_RANGES, z["ranges"].tolist()):
+        assert summary(eio.extract_from_h5_by_index(rec, a, b)) == want
