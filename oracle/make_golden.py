@@ -350,8 +350,33 @@ def make_io_golden():
     print("dsec_io.npz:", out["windows"][:, 0].tolist(), out["ranges"][:, 0].tolist())
 
 
+def make_negwins_golden():
+    """Second raster mode through the REAL generate_event_image_vectorized
+    (feasible/my_egpt_dsec_dataset/preprocess_event_images.py:58-90): the five slices of a DSEC window with the data-dependent
+    canvas and with an explicit 480x640 canvas, plus a signed-polarity window (p = -1 draws nothing in this mode)."""
+    import contextlib, importlib.util, io
+    spec = importlib.util.spec_from_file_location(
+        "ref_preprocess_event_images", os.path.join(REF, "feasible", "my_egpt_dsec_dataset", "preprocess_event_images.py"))
+    mod = importlib.util.module_from_spec(spec)
+    with contextlib.redirect_stdout(io.StringIO()):
+        spec.loader.exec_module(mod)
+    from oracle import events as oev
+    out = {}
+    for name in ("dsec_000099", "adv_signed_p"):
+        z = np.load(os.path.join(OUT, f"events_{name}.npz"))
+        x, y, p = z["x"], z["y"], z["p"]
+        starts, ends = oev.frame_bounds(len(x), 5)
+        for i, (s_, e_) in enumerate(zip(starts, ends)):
+            out[f"{name}_auto_{i}"] = mod.generate_event_image_vectorized(x[s_:e_], y[s_:e_], p[s_:e_])
+            out[f"{name}_vga_{i}"] = mod.generate_event_image_vectorized(x[s_:e_], y[s_:e_], p[s_:e_], 480, 640)
+    np.savez_compressed(os.path.join(OUT, "negwins.npz"), **out)
+    print("negwins.npz:", len(out), "frames")
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "io":
+    if len(sys.argv) > 1 and sys.argv[1] == "negwins":
+        make_negwins_golden()
+    elif len(sys.argv) > 1 and sys.argv[1] == "io":
         make_io_golden()
     elif len(sys.argv) > 1 and sys.argv[1] == "splice":
         make_splice_golden()
@@ -362,3 +387,4 @@ if __name__ == "__main__":
         make_splice_golden()
         make_clips_golden()
         make_io_golden()
+        make_negwins_golden()

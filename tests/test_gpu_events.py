@@ -285,3 +285,20 @@ def test_preprocess_arbitrary_images_wide_and_deep_filters(h, w, dev):
     got = px.view(torch.int16).cpu().numpy().view(np.uint16)[0]
     want = opp.pixel_values_bf16_bits(img)
     assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("name", ["dsec_000099", "adv_signed_p"])
+def test_negative_wins_mode_vs_reference_frames(name, dev):
+    """EGPT_RASTER_NEG_WINS through the C ABI against frames rendered by the reference's own generate_event_image_vectorized
+    (preprocess_event_images.py:58-90; tests/golden/negwins.npz): data-dependent canvas and explicit 480x640 canvas."""
+    from eventgpt_b200 import events as E, _lib
+    z = np.load(os.path.join(GOLDEN, "negwins.npz"))
+    ev, _, _ = load_golden_events(name)
+    x, y, p = _dev_events(ev, dev)
+    off = torch.tensor([0, len(ev["t"])], dtype=torch.int64, device=dev)
+    for tag, fixed in (("auto", False), ("vga", True)):
+        fr, hw, _, st = E.raster(x, y, p, off, 1, 5, 480, 640, mode=_lib.RASTER_NEG_WINS, fixed_canvas=fixed)
+        E.check_status(st, name)
+        got = E.frames_to_numpy(fr, hw)
+        for i in range(5):
+            assert np.array_equal(got[i], z[f"{name}_{tag}_{i}"]), (tag, i)

@@ -143,3 +143,17 @@ def test_clip_splitter_vs_reference_golden(name, interval, with_stamps):
         else:
             assert [len(c["t"]) for c in clips] == z[f"{name}_count"].tolist()
             assert [int(c["x"].astype(np.int64).sum()) for c in clips] == z[f"{name}_xsum"].tolist()
+
+
+@pytest.mark.parametrize("name", ["dsec_000099", "adv_signed_p"])
+def test_negative_wins_raster_vs_reference_golden(name):
+    """oracle.events.generate_event_image_negwins against the REAL generate_event_image_vectorized
+    (preprocess_event_images.py:58-90; tests/golden/negwins.npz from `python -m oracle.make_golden negwins`)."""
+    from oracle import events as oev
+    z = np.load(os.path.join(GOLDEN, "negwins.npz"))
+    e = np.load(os.path.join(GOLDEN, f"events_{name}.npz"))
+    x, y, p = e["x"], e["y"], e["p"]
+    starts, ends = oev.frame_bounds(len(x), 5)
+    for i, (s, t) in enumerate(zip(starts, ends)):
+        assert np.array_equal(oev.generate_event_image_negwins(x[s:t], y[s:t], p[s:t]), z[f"{name}_auto_{i}"])
+        assert np.array_equal(oev.generate_event_image_negwins(x[s:t], y[s:t], p[s:t], 480, 640), z[f"{name}_vga_{i}"])
