@@ -203,7 +203,7 @@ def run_ours(args, rank, world, local_rank):
 
     from eventgpt_b200.pipeline import VisualTokenStream
     stream = VisualTokenStream(fe, n_ev, hi - lo, (H, W))
-    gather = (lambda tok: dist.all_gather_into_tensor(gathered[0], tok)) if world > 1 else None
+    gather = (lambda tok, slot: dist.all_gather_into_tensor(gathered[slot], tok, async_op=True)) if world > 1 else None
 
     def step_e2e():
         # public host-fed API: pinned host events in, tokens out to pinned host memory, every step; the H2D of
@@ -246,7 +246,7 @@ def run_ours(args, rank, world, local_rank):
         step_e2e()
     stream.drain()
     # the last batch's D2H is inside the timed region: the compute stream waits for the copy-out stream
-    e2e_ms = timed(step_e2e, args.steps, tail=lambda: torch.cuda.current_stream(dev).wait_stream(stream.s_out))
+    e2e_ms = timed(step_e2e, args.steps, tail=stream.join)
     stream.drain()
 
     # per-kernel-family device time, CUDA events on the launching stream (second pass, K steps)

@@ -34,11 +34,15 @@ class VisualTokenStream:
         self.ev_h2d = [torch.cuda.Event() for _ in range(depth)]
         self.ev_done = [torch.cuda.Event() for _ in range(depth)]
         self.ev_d2h = [torch.cuda.Event() for _ in range(depth)]
+        self.posted = [None] * depth
         self.count = 0
 
     def submit(self, hx, hy, hp, hoff, post=None):
         """Enqueue one batch (pinned host tensors: x, y uint16; p uint8; window offsets int64 [B+1]).
-        Returns the slot whose pinned ``htok[slot][:B]`` holds the tokens once ``wait(slot)`` returns."""
+        Returns the slot whose pinned ``htok[slot][:B]`` holds the tokens once ``wait(slot)`` returns.
+        ``post(tokens, slot)``, if given, runs right after the batch's compute was enqueued (e.g. the final all_gather of a
+        multi-GPU job); it may return an asynchronous work handle (``.wait()``), which is waited for before the slot's token
+        buffer is written again and in ``drain``."""
         i, s = self.count, self.count % self.depth
         self.count += 1
         n, B = hx.numel(), hoff.numel() - 1
@@ -56,10 +60,13 @@ class VisualTokenStream:
         compute.wait_event(self.ev_h2d[s])
         if i >= self.depth:
             compute.wait_event(self.ev_d2h[s])             # slot's token buffer was read out
+        if self.posted[s] is not None:
+            self.posted[s].wait()                          # ... also by the slot's asynchronous post step
+            self.posted[s] = None
         self.fe.visual_tokens(self.dx[s][:n], self.dy[s][:n], self.dp[s][:n], self.doff[s][:B + 1], self.sensor,
                               n_frames=self.n_frames, out=self.tok[s][:B], check_flags=False)
         if post is not None:
-            post(self.tok[s][:B])                          # e.g. the final all_gather of a multi-GPU job
+            self.posted[s] = post(self.tok[s][:B], s)      # e.g. the final all_gather of a multi-GPU job
         self.ev_done[s].record(compute)
         self.s_out.wait_event(self.ev_done[s])
         with torch.cuda.stream(self.s_out):
@@ -71,6 +78,19 @@ class VisualTokenStream:
         self.ev_d2h[slot].synchronize()
         return self.htok[slot]
 
+    def join(self):
+        """Stream-level join (no host synchronisation): the caller's current stream waits for every copy-out and post step
+        enqueued so far -- what a timed region records its end event after."""
+        for s in range(self.depth):
+            if self.posted[s] is not None:
+                self.posted[s].wait()
+                self.posted[s] = None
+        torch.cuda.current_stream(self.dev).wait_stream(self.s_out)
+
     def drain(self):
+        for s in range(self.depth):
+            if self.posted[s] is not None:
+                self.posted[s].wait()
+                self.posted[s] = None
         self.s_out.synchronize()
         torch.cuda.current_stream(self.dev).synchronize()
