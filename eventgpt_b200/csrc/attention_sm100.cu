@@ -94,18 +94,6 @@ __device__ __forceinline__ float ex2(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-// 2^x for x <= ~8 on the FMA/ALU pipes (Cody-Waite split + cubic).  Relative error < 1e-4, far below the bf16
-// rounding P undergoes anyway.
-__device__ __forceinline__ float ex2_poly(float x) {
-  x = fmaxf(x, -126.0f);
-  const float t = x + 12582912.0f;                 // 1.5 * 2^23: rounds x to the nearest integer n
-  const float n = t - 12582912.0f;
-  const float f = x - n;                           // [-0.5, 0.5]
-  float p = fmaf(f, 0.0555041f, 0.2402265f);
-  p = fmaf(p, f, 0.6931472f);
-  p = fmaf(p, f, 1.0f);
-  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
-}
 // packed fp32x2 arithmetic (sm_100): one issue slot for two lanes of fma / add
 __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
   float2 d;
@@ -120,7 +108,9 @@ __device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
       : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)));
   return d;
 }
-// two cubic exp2 at once (same scheme as ex2_poly)
+// 2^x for x <= ~8 on the FMA pipe, two at once: Cody-Waite split (adding 1.5 * 2^23 rounds x to the nearest integer n) and a
+// cubic in f = x - n in [-0.5, 0.5]; the integer part goes into the exponent field.  Relative error < 1e-4, far below the bf16
+// rounding P undergoes anyway.
 __device__ __forceinline__ float2 ex2_poly2(float2 x) {
   x.x = fmaxf(x.x, -126.0f); x.y = fmaxf(x.y, -126.0f);
   const float2 t = fadd2(x, make_float2(12582912.0f, 12582912.0f));
@@ -157,9 +147,6 @@ __device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, u
       "}"
       ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
-}
-__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
 struct Bars {
