@@ -5,19 +5,39 @@
 // reference, plus the "negative wins" raster of
 // feasible/my_egpt_dsec_dataset/preprocess_event_images.py:58-90.
 //
-// Rasterisation is "last event at a pixel wins", which is not commutative.  It
-// is made order-free with a key  ((index_in_slice + 1) << 1) | (p != 0)  and an
-// atomicMax into a per-frame uint32 key plane; a second kernel turns keys into
-// RGB.  Key planes are scratch: they are processed in chunks of windows small
-// enough to stay resident in the 126 MB L2, so DRAM traffic stays at the
-// algorithmic 5 B/event read + 3 B/pixel written.
+// Rasterisation is "last event at a pixel wins", which is not commutative.  The per-event
+// operation is a PLAIN one-byte shared-memory store inside a CTA that owns a band of rows of
+// one frame (no atomic per event):
+//   * a frame is cut into R bands of rows so that one byte per pixel of a band fits in the
+//     shared memory of one SM (640x480 -> 2 bands of 240 rows, 1280x720 -> 5 bands of 144);
+//     a long slice is also cut into up to K consecutive event ranges.  One CTA per
+//     (frame, band, event range) streams its range with 128-bit loads (8 events per load),
+//     keeps the events of its band and drops the others after two instructions;
+//   * events are consumed in batches of 16 384 with a CTA barrier between batches, so order
+//     ACROSS batches is free.  INSIDE a batch every warp owns consecutive 256-event chunks
+//     and stores the byte  (chunk_rank+1)<<1 | (p != 0).  After the barrier each thread reads
+//     its cells back: a cell holding a lower rank (an earlier chunk overwrote a later one) or
+//     the same rank with the other polarity (two events of one chunk on one pixel) is
+//     repaired -- the warp finds the latest event of its chunk on that pixel with one
+//     shuffle/reduce step -- and re-checked until no thread objects.  With uniformly spread
+//     events a few pixels per batch need this; a hot pixel costs one step per chunk;
+//   * the finished band leaves as 2 bits per pixel (0 untouched, 2 blue, 3 red) into the
+//     caller's scratch; the second kernel overlays the K partial planes of a frame in range
+//     order and writes packed RGB at the data-dependent pitch.
+// DRAM traffic is the algorithmic 5 B/event + 3 B/pixel plus 2 x 0.25 B/pixel/range of scratch.
 #include "common.cuh"
 #include <mutex>
 
 namespace egpt {
 
-constexpr int kScatterThreads = 256;
-constexpr size_t kKeyPlaneL2Budget = 48u << 20;   // bytes of key planes kept live per chunk
+constexpr int kTileThreads = 512;
+constexpr int kTileWarps = kTileThreads / 32;
+constexpr int kGroupsPerBatch = 4;                              // 8-event groups per thread per batch
+constexpr int kBatchGroups = kTileThreads * kGroupsPerBatch;    // 2048 groups = 16 384 events between barriers
+constexpr int kMaxPlaneBytes = 200 * 1024;                      // band plane held in shared memory
+constexpr int kMaxRanges = 12;                                  // K: event ranges per slice
+constexpr long long kMinRangeGroups = 4096;                     // a range is at least 32 768 events
+constexpr unsigned kNoCell = 0xffffffffu;
 
 struct SliceInfo {
   long long start, end;
@@ -33,135 +53,285 @@ __device__ __forceinline__ SliceInfo slice_bounds(const int64_t* __restrict__ of
   return r;
 }
 
-__device__ __forceinline__ void emit_event(unsigned x, unsigned y, unsigned pz, unsigned key_last, int mode,
-                                           int H, int W, uint32_t* __restrict__ plane, int32_t* __restrict__ counts,
-                                           unsigned& mx, unsigned& my, unsigned& flags) {
-  if (x >= (unsigned)W || y >= (unsigned)H) { flags |= EGPT_FLAG_OUT_OF_RANGE; return; }
-  mx = max(mx, x);
-  my = max(my, y);
-  unsigned pix = y * (unsigned)W + x;
-  if (mode == EGPT_RASTER_LAST_WINS) {
-    atomicMax(plane + pix, key_last | (pz ? 0u : 1u));
-    if (counts) atomicAdd(counts + (size_t)(pz ? 0 : 1) * H * W + pix, 1);
+// how a frame is cut into row bands, and how much scratch one partial plane takes
+struct TilePlan {
+  int band_rows, R, K;
+  unsigned plane_smem;      // bytes of shared memory per CTA (one byte per pixel of a band)
+  unsigned plane_words;     // 32-bit words of one 2-bit-per-pixel partial plane (whole frame), multiple of 4
+};
+
+static bool make_tile_plan(int H, int W, long long frames, TilePlan* pl) {
+  int rows_fit = kMaxPlaneBytes / W;
+  if (rows_fit >= H) {
+    pl->band_rows = H;
+    pl->R = 1;
+  } else {
+    rows_fit &= ~15;                                  // bands start on a 16-pixel boundary of the 2-bit plane
+    if (rows_fit < 16) return false;
+    int R = (H + rows_fit - 1) / rows_fit;
+    int rows = ((H + R - 1) / R + 15) & ~15;
+    pl->band_rows = rows;
+    pl->R = (H + rows - 1) / rows;
   }
+  pl->plane_smem = (unsigned)(((size_t)pl->band_rows * W + 15) & ~(size_t)15);
+  pl->plane_words = (unsigned)((((size_t)H * W + 15) / 16 + 3) & ~(size_t)3);
+  // enough CTAs for two full waves of the machine when the batch itself is small
+  long long items = frames * pl->R;
+  long long K = (2LL * kNumSMs) / items;
+  if (K < 1) K = 1;
+  if (K > kMaxRanges) K = kMaxRanges;
+  pl->K = (int)K;
+  return true;
 }
 
-// One CTA column per slice (blockIdx.y); CTAs of a column stride over the slice.
-// FAST: x,y uint16 and p uint8 with 16/16/8-byte aligned bases -> 128-bit loads of 8 events.
-template <bool FAST>
-__global__ void __launch_bounds__(kScatterThreads)
-raster_scatter_kernel(const void* __restrict__ xv, const void* __restrict__ yv, const void* __restrict__ pv,
-                      int xdt, int ydt, int pdt, const int64_t* __restrict__ offsets,
-                      int window0, int n_frames, int mode, int H, int W, int fixed_canvas,
-                      uint32_t* __restrict__ planes, int32_t* __restrict__ out_hw,
-                      int32_t* __restrict__ out_counts, int32_t* __restrict__ status) {
-  const int local_slice = blockIdx.y;
-  const int window = window0 + local_slice / n_frames;
-  const int fi = local_slice % n_frames;
-  const int frame = window * n_frames + fi;
-  const SliceInfo sl = slice_bounds(offsets, window, fi, n_frames);
-  uint32_t* plane = planes + (size_t)local_slice * H * W;
-  int32_t* counts = out_counts ? out_counts + (size_t)frame * 2 * H * W : nullptr;
-  unsigned mx = 0, my = 0, flags = 0;
-  bool any = false;
+// number of event ranges a slice of `ng` 8-event groups is really cut into (same rule in both kernels)
+__device__ __forceinline__ int ranges_of(long long ng, int K) {
+  if (ng <= 0) return 0;
+  long long k = (ng + kMinRangeGroups - 1) / kMinRangeGroups;
+  return (int)(k < K ? k : K);
+}
 
+struct RasterArgs {
+  const void *x, *y, *p;
+  int xdt, ydt, pdt;
+  const int64_t* offsets;
+  int n_frames, H, W, fixed_canvas;
+  TilePlan plan;
+  uint32_t* scratch;        // [frame][K][plane_words]
+  int32_t* out_hw;
+  int32_t* out_counts;
+  int32_t* status;
+};
+
+// eight consecutive events as loaded: x, y as 8 x u16, p as 8 x u8, and which of the eight belong to the slice
+struct EventGroup {
+  uint4 x, y;
+  uint2 p;
+  unsigned valid;
+};
+
+template <bool FAST>
+__device__ __forceinline__ EventGroup load_group(const RasterArgs& a, long long g, long long g_end, const SliceInfo& sl,
+                                                 unsigned& flags) {
+  EventGroup e;
+  e.x = make_uint4(0, 0, 0, 0); e.y = make_uint4(0, 0, 0, 0); e.p = make_uint2(0, 0);
+  e.valid = 0;
+  if (g >= g_end) return e;
+  const long long base = g << 3;
+  if (FAST && base >= sl.start && base + 8 <= sl.end) {
+    e.x = __ldg(reinterpret_cast<const uint4*>(a.x) + g);
+    e.y = __ldg(reinterpret_cast<const uint4*>(a.y) + g);
+    e.p = __ldg(reinterpret_cast<const uint2*>(a.p) + g);
+    e.valid = 0xffu;
+    return e;
+  }
+  // slice boundary or generic element types: element loads, never outside [start, end)
+  unsigned xw[4] = {0, 0, 0, 0}, yw[4] = {0, 0, 0, 0}, pw[2] = {0, 0};
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const long long i = base + j;
+    if (i < sl.start || i >= sl.end) continue;
+    long long xl, yl, pl;
+    if (FAST) {
+      xl = ((const uint16_t*)a.x)[i]; yl = ((const uint16_t*)a.y)[i]; pl = ((const uint8_t*)a.p)[i];
+    } else {
+      xl = load_int(a.x, a.xdt, i); yl = load_int(a.y, a.ydt, i); pl = load_int(a.p, a.pdt, i);
+    }
+    if (xl < 0 || yl < 0 || xl >= a.W || yl >= a.H) { flags |= EGPT_FLAG_OUT_OF_RANGE; continue; }
+    xw[j >> 1] |= (unsigned)xl << ((j & 1) * 16);
+    yw[j >> 1] |= (unsigned)yl << ((j & 1) * 16);
+    pw[j >> 2] |= (pl == 0 ? 0u : (pl == 1 ? 1u : 2u)) << ((j & 3) * 8);
+    e.valid |= 1u << j;
+  }
+  e.x = make_uint4(xw[0], xw[1], xw[2], xw[3]);
+  e.y = make_uint4(yw[0], yw[1], yw[2], yw[3]);
+  e.p = make_uint2(pw[0], pw[1]);
+  return e;
+}
+
+// 4 one-byte cells -> 4 two-bit codes: 0 untouched, 2 | (cell & 1) otherwise
+__device__ __forceinline__ unsigned pack_cells4(unsigned w) {
+  const unsigned nz = (((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w) & 0x80808080u;
+  const unsigned c = (nz >> 6) | (w & 0x01010101u);
+  return (c * 0x01041040u) >> 24;
+}
+
+// One CTA per (frame, band of rows, event range).  MODE 0: last event wins; MODE 1: negative wins.
+template <bool FAST, int MODE>
+__global__ void __launch_bounds__(kTileThreads, 1)
+raster_tile_kernel(const __grid_constant__ RasterArgs a) {
+  extern __shared__ __align__(16) uint8_t plane[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int R = a.plan.R, K = a.plan.K, H = a.H, W = a.W;
+  const long long item = blockIdx.x;
+  const int band = (int)(item % R), range = (int)((item / R) % K);
+  const long long frame = item / ((long long)R * K);
+  const int window = (int)(frame / a.n_frames), fi = (int)(frame % a.n_frames);
+  const SliceInfo sl = slice_bounds(a.offsets, window, fi, a.n_frames);
   if (sl.end <= sl.start) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(status, EGPT_FLAG_EMPTY_SLICE);
+    if (band == 0 && range == 0 && tid == 0) atomicOr(a.status, EGPT_FLAG_EMPTY_SLICE);
     return;
   }
+  const long long g0 = sl.start >> 3, ng = ((sl.end + 7) >> 3) - g0;
+  const int n_ranges = ranges_of(ng, K);
+  if (range >= n_ranges) return;
+  const long long g_begin = g0 + ng * range / n_ranges, g_end = g0 + ng * (range + 1) / n_ranges;
+  const unsigned y0 = (unsigned)band * a.plan.band_rows;
+  const unsigned bh = min((unsigned)a.plan.band_rows, (unsigned)H - y0);
+  int32_t* counts = a.out_counts ? a.out_counts + (size_t)frame * 2 * H * W : nullptr;
 
-  if (FAST) {
-    // groups of 8 events; every thread takes kUnroll groups per trip with all its loads issued first
-    // (the kernel is bound by load latency, not by the L2 reductions)
-    constexpr int kUnroll = 4;
-    const long long g0 = sl.start >> 3, g1 = (sl.end + 7) >> 3;
-    const long long stride = (long long)gridDim.x * kScatterThreads;
-    for (long long gb = g0 + (long long)blockIdx.x * kScatterThreads + threadIdx.x; gb < g1; gb += stride * kUnroll) {
-      uint4 xs[kUnroll], ys[kUnroll];
-      uint2 ps[kUnroll];
-      bool whole[kUnroll];
+  for (unsigned i = tid; i < a.plan.plane_smem / 16; i += kTileThreads) reinterpret_cast<uint4*>(plane)[i] = make_uint4(0, 0, 0, 0);
+
+  unsigned mx = 0, my = 0, flags = 0;
+  bool any = false;
+  EventGroup ev[kGroupsPerBatch];
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        const long long g = gb + u * stride, base = g << 3;
-        whole[u] = g < g1 && base >= sl.start && base + 8 <= sl.end;
-        if (whole[u]) {
-          xs[u] = __ldg(reinterpret_cast<const uint4*>(xv) + g);
-          ys[u] = __ldg(reinterpret_cast<const uint4*>(yv) + g);
-          ps[u] = __ldg(reinterpret_cast<const uint2*>(pv) + g);
+  for (int g = 0; g < kGroupsPerBatch; ++g)
+    ev[g] = load_group<FAST>(a, g_begin + (long long)(g * kTileWarps + warp) * 32 + lane, g_end, sl, flags);
+  __syncthreads();
+
+  for (long long gb = g_begin; gb < g_end; gb += kBatchGroups) {
+    // ---- store: cell = rank of the 256-event chunk within the batch, and the polarity ------------------
+    unsigned cell[kGroupsPerBatch][8];          // (pixel << 1) | polarity bit, or kNoCell
+#pragma unroll
+    for (int g = 0; g < kGroupsPerBatch; ++g) {
+      const unsigned rank2 = (unsigned)(g * kTileWarps + warp + 1) << 1;
+      const unsigned xw[4] = {ev[g].x.x, ev[g].x.y, ev[g].x.z, ev[g].x.w};
+      const unsigned yw[4] = {ev[g].y.x, ev[g].y.y, ev[g].y.z, ev[g].y.w};
+      const unsigned pw[2] = {ev[g].p.x, ev[g].p.y};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const unsigned xv = (xw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
+        const unsigned yv = (yw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
+        const unsigned pb = (pw[j >> 2] >> ((j & 3) * 8)) & 0xffu;
+        cell[g][j] = kNoCell;
+        if (!((ev[g].valid >> j) & 1u)) continue;
+        if (xv >= (unsigned)W || yv >= (unsigned)H) { flags |= EGPT_FLAG_OUT_OF_RANGE; continue; }
+        const unsigned yy = yv - y0;
+        if (yy >= bh) continue;                                    // another band's event
+        any = true;
+        mx = max(mx, xv); my = max(my, yv);
+        const unsigned pix = yy * (unsigned)W + xv;
+        if (MODE == EGPT_RASTER_LAST_WINS) {
+          const unsigned pol = pb != 0;
+          plane[pix] = (uint8_t)(rank2 | pol);
+          cell[g][j] = (pix << 1) | pol;
+          if (counts) atomicAdd(counts + (size_t)pol * H * W + (size_t)yv * W + xv, 1);
+        } else if (pb <= 1) {                                      // p == 0: negative (wins), p == 1: positive
+          const unsigned val = pb ? 0x01u : 0xfeu;
+          if (plane[pix] < val) plane[pix] = (uint8_t)val;
+          cell[g][j] = (pix << 1) | pb;
         }
       }
+    }
+    // the next batch's events travel while this one is checked
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        const long long g = gb + u * stride, base = g << 3;
-        if (g >= g1) break;
-        unsigned xw[4], yw[4], pw[2];
-        if (whole[u]) {
-          xw[0] = xs[u].x; xw[1] = xs[u].y; xw[2] = xs[u].z; xw[3] = xs[u].w;
-          yw[0] = ys[u].x; yw[1] = ys[u].y; yw[2] = ys[u].z; yw[3] = ys[u].w;
-          pw[0] = ps[u].x; pw[1] = ps[u].y;
+    for (int g = 0; g < kGroupsPerBatch; ++g)
+      ev[g] = load_group<FAST>(a, gb + kBatchGroups + (long long)(g * kTileWarps + warp) * 32 + lane, g_end, sl, flags);
+    __syncthreads();
+
+    // ---- check: does every cell hold the latest event of the batch on its pixel? --------------------------
+    unsigned bad = 0;
+#pragma unroll
+    for (int g = 0; g < kGroupsPerBatch; ++g) {
+      const unsigned rank2 = (unsigned)(g * kTileWarps + warp + 1) << 1;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (cell[g][j] == kNoCell) continue;
+        const unsigned c = plane[cell[g][j] >> 1];
+        if (MODE == EGPT_RASTER_LAST_WINS) {
+          const unsigned val = rank2 | (cell[g][j] & 1u);
+          if (c != val && c <= (rank2 | 1u)) bad |= 1u << (g * 8 + j);
         } else {
-          // boundary group: element loads, never outside [start, end)
-          xw[0] = xw[1] = xw[2] = xw[3] = yw[0] = yw[1] = yw[2] = yw[3] = pw[0] = pw[1] = 0;
+          if (c < ((cell[g][j] & 1u) ? 0x01u : 0xfeu)) bad |= 1u << (g * 8 + j);
+        }
+      }
+    }
+    while (__syncthreads_or(bad != 0)) {
+      unsigned recheck = 0;
+      if (MODE == EGPT_RASTER_LAST_WINS) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const long long i = base + j;
-            if (i < sl.start || i >= sl.end) continue;
-            xw[j >> 1] |= (unsigned)((const uint16_t*)xv)[i] << ((j & 1) * 16);
-            yw[j >> 1] |= (unsigned)((const uint16_t*)yv)[i] << ((j & 1) * 16);
-            pw[j >> 2] |= (unsigned)((const uint8_t*)pv)[i] << ((j & 3) * 8);
+        for (int g = 0; g < kGroupsPerBatch; ++g) {
+          const unsigned rank2 = (unsigned)(g * kTileWarps + warp + 1) << 1;
+          unsigned gm = (bad >> (g * 8)) & 0xffu;
+          // one step per disputed pixel of this warp's chunk: the latest event of the chunk on it writes
+          for (;;) {
+            const unsigned ballot = __ballot_sync(0xffffffffu, gm != 0);
+            if (!ballot) break;
+            unsigned mine = 0;
+#pragma unroll
+            for (int j = 7; j >= 0; --j) if ((gm >> j) & 1u) mine = cell[g][j] >> 1;
+            const unsigned P = __shfl_sync(0xffffffffu, mine, __ffs(ballot) - 1);
+            int best = -1;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (cell[g][j] != kNoCell && (cell[g][j] >> 1) == P) { best = j; gm &= ~(1u << j); }
+            const int key = best >= 0 ? lane * 8 + best : -1;
+            const int top = __reduce_max_sync(0xffffffffu, key);
+            if (best >= 0 && key == top) {
+              unsigned pol = 0;
+#pragma unroll
+              for (int j = 0; j < 8; ++j) if (j == best) pol = cell[g][j] & 1u;
+              if (plane[P] <= (rank2 | 1u)) plane[P] = (uint8_t)(rank2 | pol);
+              recheck |= 1u << (g * 8 + best);
+            }
           }
         }
+      } else {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const long long i = base + j;
-          if (i < sl.start || i >= sl.end) continue;
-          const unsigned x = (xw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-          const unsigned y = (yw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-          const unsigned p = (pw[j >> 2] >> ((j & 3) * 8)) & 0xffu;
-          any = true;
-          if (mode == EGPT_RASTER_LAST_WINS) {
-            emit_event(x, y, p == 0, (unsigned)(i - sl.start + 1) << 1, mode, H, W, plane, counts, mx, my, flags);
-          } else {
-            if (x >= (unsigned)W || y >= (unsigned)H) { flags |= EGPT_FLAG_OUT_OF_RANGE; continue; }
-            mx = max(mx, x); my = max(my, y);
-            if (p == 0) atomicMax(plane + y * (unsigned)W + x, 2u);
-            else if (p == 1) atomicMax(plane + y * (unsigned)W + x, 1u);
+        for (int g = 0; g < kGroupsPerBatch; ++g)
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if ((bad >> (g * 8 + j)) & 1u) {
+              const unsigned val = (cell[g][j] & 1u) ? 0x01u : 0xfeu;
+              if (plane[cell[g][j] >> 1] < val) plane[cell[g][j] >> 1] = (uint8_t)val;
+              recheck |= 1u << (g * 8 + j);
+            }
+      }
+      __syncthreads();
+      bad = 0;
+      if (recheck) {
+#pragma unroll
+        for (int g = 0; g < kGroupsPerBatch; ++g) {
+          const unsigned rank2 = (unsigned)(g * kTileWarps + warp + 1) << 1;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (!((recheck >> (g * 8 + j)) & 1u)) continue;
+            const unsigned c = plane[cell[g][j] >> 1];
+            if (MODE == EGPT_RASTER_LAST_WINS) {
+              const unsigned val = rank2 | (cell[g][j] & 1u);
+              if (c != val && c <= (rank2 | 1u)) bad |= 1u << (g * 8 + j);
+            } else {
+              if (c < ((cell[g][j] & 1u) ? 0x01u : 0xfeu)) bad |= 1u << (g * 8 + j);
+            }
           }
         }
       }
     }
-  } else {
-    for (long long i = sl.start + (long long)blockIdx.x * kScatterThreads + threadIdx.x; i < sl.end;
-         i += (long long)gridDim.x * kScatterThreads) {
-      const long long xl = load_int(xv, xdt, i), yl = load_int(yv, ydt, i), pl = load_int(pv, pdt, i);
-      any = true;
-      if (xl < 0 || yl < 0 || xl >= W || yl >= H) { flags |= EGPT_FLAG_OUT_OF_RANGE; continue; }
-      const unsigned x = (unsigned)xl, y = (unsigned)yl;
-      if (mode == EGPT_RASTER_LAST_WINS) {
-        emit_event(x, y, pl == 0, (unsigned)(i - sl.start + 1) << 1, mode, H, W, plane, counts, mx, my, flags);
-      } else {
-        mx = max(mx, x); my = max(my, y);
-        if (pl == 0) atomicMax(plane + y * (unsigned)W + x, 2u);
-        else if (pl == 1) atomicMax(plane + y * (unsigned)W + x, 1u);
-      }
+  }
+
+  // ---- the band leaves as 2 bits per pixel ------------------------------------------------------------
+  {
+    uint32_t* dst = a.scratch + ((size_t)frame * K + range) * a.plan.plane_words + ((size_t)y0 * W >> 4);
+    const unsigned words = (unsigned)(((size_t)bh * W + 15) >> 4);
+    for (unsigned i = tid; i < words; i += kTileThreads) {
+      const uint4 c = reinterpret_cast<const uint4*>(plane)[i];
+      dst[i] = pack_cells4(c.x) | (pack_cells4(c.y) << 8) | (pack_cells4(c.z) << 16) | (pack_cells4(c.w) << 24);
     }
   }
 
   // canvas extent = (max y + 1, max x + 1) of the slice (common/common.py:65)
-  if (!fixed_canvas) {
+  if (!a.fixed_canvas) {
     unsigned vx = any ? mx + 1 : 0, vy = any ? my + 1 : 0;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      vx = max(vx, __shfl_xor_sync(0xffffffffu, vx, o));
-      vy = max(vy, __shfl_xor_sync(0xffffffffu, vy, o));
-    }
-    if ((threadIdx.x & 31) == 0 && vx) {
-      atomicMax(out_hw + 2 * frame + 0, (int)vy);
-      atomicMax(out_hw + 2 * frame + 1, (int)vx);
+    vx = __reduce_max_sync(0xffffffffu, vx);
+    vy = __reduce_max_sync(0xffffffffu, vy);
+    if (lane == 0 && vx) {
+      atomicMax(a.out_hw + 2 * frame + 0, (int)vy);
+      atomicMax(a.out_hw + 2 * frame + 1, (int)vx);
     }
   }
   flags = __reduce_or_sync(0xffffffffu, flags);
-  if ((threadIdx.x & 31) == 0 && flags) atomicOr(status, (int)flags);
+  if (lane == 0 && flags) atomicOr(a.status, (int)flags);
 }
 
 __global__ void set_fixed_hw_kernel(int32_t* __restrict__ hw, int n, int H, int W) {
@@ -169,45 +339,54 @@ __global__ void set_fixed_hw_kernel(int32_t* __restrict__ hw, int n, int H, int 
   if (i < n) { hw[2 * i] = H; hw[2 * i + 1] = W; }
 }
 
-__device__ __forceinline__ unsigned rgb_of_key(unsigned key) {
-  // little-endian byte triple: white 255,255,255; red 255,0,0 (odd key); blue 0,0,255
-  return key == 0 ? 0x00ffffffu : ((key & 1u) ? 0x000000ffu : 0x00ff0000u);
+__device__ __forceinline__ unsigned rgb_of_code(unsigned code) {
+  // little-endian byte triple: white 255,255,255 (0); blue 0,0,255 (2); red 255,0,0 (3)
+  return code == 0 ? 0x00ffffffu : ((code & 1u) ? 0x000000ffu : 0x00ff0000u);
 }
 
-// keys -> packed RGB; 16 pixels (64 B of keys -> 48 B of RGB) per thread.
+// a later range's pixels lie over an earlier range's
+__device__ __forceinline__ unsigned overlay_codes(unsigned under, unsigned over) {
+  const unsigned m = ((over >> 1) & 0x55555555u) * 3u;
+  return (under & ~m) | (over & m);
+}
+
+// partial planes -> packed RGB; 16 pixels (one word of codes per range -> 48 B of RGB) per thread.
 __global__ void __launch_bounds__(256)
-raster_colourise_kernel(const uint32_t* __restrict__ planes, const int32_t* __restrict__ out_hw,
-                        int frame0, int H, int W, uint8_t* __restrict__ out_frames, size_t frame_stride) {
-  const int local = blockIdx.y;
-  const int frame = frame0 + local;
+raster_colourise_kernel(const uint32_t* __restrict__ scratch, const int32_t* __restrict__ out_hw,
+                        const int64_t* __restrict__ offsets, int n_frames, int K, unsigned plane_words, int W,
+                        uint8_t* __restrict__ out_frames, size_t frame_stride) {
+  const long long frame = blockIdx.y;
   const int h = out_hw[2 * frame], w = out_hw[2 * frame + 1];
   const long long npix = (long long)h * w;
   if (npix == 0) return;
-  const uint32_t* plane = planes + (size_t)local * H * W;
+  const SliceInfo sl = slice_bounds(offsets, (int)(frame / n_frames), (int)(frame % n_frames), n_frames);
+  const int n_ranges = sl.end > sl.start ? ranges_of(((sl.end + 7) >> 3) - (sl.start >> 3), K) : 0;
+  const uint32_t* planes = scratch + (size_t)frame * K * plane_words;
   uint8_t* dst = out_frames + (size_t)frame * frame_stride;
   const long long ngroups = (npix + 15) >> 4;
   for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < ngroups;
        g += (long long)gridDim.x * blockDim.x) {
     const long long p0 = g << 4;
     unsigned c[16];
-    if (w == W && p0 + 16 <= npix && ((reinterpret_cast<uintptr_t>(plane + p0) & 15) == 0)) {
-      const uint4* kp = reinterpret_cast<const uint4*>(plane + p0);
+    if (w == W) {
+      unsigned m = 0;
+      for (int k = 0; k < n_ranges; ++k) m = overlay_codes(m, planes[(size_t)k * plane_words + g]);
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const uint4 k = kp[q];
-        c[4 * q + 0] = rgb_of_key(k.x); c[4 * q + 1] = rgb_of_key(k.y);
-        c[4 * q + 2] = rgb_of_key(k.z); c[4 * q + 3] = rgb_of_key(k.w);
-      }
+      for (int j = 0; j < 16; ++j) c[j] = rgb_of_code((m >> (2 * j)) & 3u);
     } else {
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
         const long long p = p0 + j;
-        unsigned key = 0;
+        unsigned code = 0;
         if (p < npix) {
           const int yy = (int)(p / w), xx = (int)(p - (long long)yy * w);
-          key = plane[(size_t)yy * W + xx];
+          const size_t q = (size_t)yy * W + xx;
+          for (int k = 0; k < n_ranges; ++k) {
+            const unsigned v = (planes[(size_t)k * plane_words + (q >> 4)] >> ((q & 15) * 2)) & 3u;
+            if (v) code = v;
+          }
         }
-        c[j] = rgb_of_key(key);
+        c[j] = rgb_of_code(code);
       }
     }
     if (p0 + 16 <= npix) {
@@ -386,14 +565,6 @@ static SplitPlan make_split_plan(long long n, int max_windows) {
   return pl;
 }
 
-static int raster_chunk_windows(int n_windows, int n_frames, int H, int W) {
-  const size_t per_window = (size_t)n_frames * H * W * sizeof(uint32_t);
-  size_t c = kKeyPlaneL2Budget / per_window;
-  if (c < 1) c = 1;
-  if (c > (size_t)n_windows) c = n_windows;
-  return (int)c;
-}
-
 }  // namespace egpt
 
 using namespace egpt;
@@ -402,67 +573,92 @@ extern "C" size_t egpt_raster_frame_stride(int H, int W) { return align_up((size
 
 extern "C" size_t egpt_raster_workspace_bytes(int n_windows, int n_frames, int H, int W) {
   if (n_windows <= 0 || n_frames <= 0 || H <= 0 || W <= 0) return 0;
-  const int cw = raster_chunk_windows(n_windows, n_frames, H, W);
-  return align_up((size_t)cw * n_frames * H * W * sizeof(uint32_t), 1024) + 1024;
+  TilePlan pl;
+  if (!make_tile_plan(H, W, (long long)n_windows * n_frames, &pl)) return 0;
+  return (size_t)n_windows * n_frames * pl.K * pl.plane_words * sizeof(uint32_t) + 1024;
 }
 
-extern "C" int egpt_raster(const void* x, const void* y, const void* p, int x_dtype, int y_dtype, int p_dtype,
-                           const int64_t* window_offsets, int n_windows, int n_frames, int mode, int H, int W,
-                           int fixed_canvas, uint8_t* out_frames, int32_t* out_hw, int32_t* out_counts,
-                           int32_t* status, void* workspace, size_t workspace_bytes, void* stream_) {
-  cudaStream_t stream = (cudaStream_t)stream_;
+namespace egpt {
+template <bool FAST, int MODE>
+static int launch_tiles(const RasterArgs& a, long long items, cudaStream_t stream) {
+  EGPT_CUDA(cudaFuncSetAttribute(raster_tile_kernel<FAST, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)a.plan.plane_smem));
+  raster_tile_kernel<FAST, MODE><<<(unsigned)items, kTileThreads, a.plan.plane_smem, stream>>>(a);
+  EGPT_LAUNCH_CHECK();
+  return EGPT_OK;
+}
+
+// shrink_to_fit: use fewer event ranges per slice when the scratch is smaller than the query asks for
+static int raster_impl(const void* x, const void* y, const void* p, int x_dtype, int y_dtype, int p_dtype,
+                       const int64_t* window_offsets, int n_windows, int n_frames, int mode, int H, int W,
+                       int fixed_canvas, uint8_t* out_frames, int32_t* out_hw, int32_t* out_counts, int32_t* status,
+                       void* workspace, size_t workspace_bytes, bool shrink_to_fit, cudaStream_t stream) {
   EGPT_CHECK_ARG(x && y && p && window_offsets && out_frames && out_hw && status && workspace,
                  "egpt_raster: null pointer argument");
   EGPT_CHECK_ARG(n_windows > 0 && n_frames > 0, "egpt_raster: n_windows=%d n_frames=%d must be positive", n_windows, n_frames);
-  EGPT_CHECK_ARG(H > 0 && W > 0 && (long long)H * W < (1LL << 31) / 4, "egpt_raster: bad canvas capacity %dx%d", H, W);
+  EGPT_CHECK_ARG(H > 0 && W > 0 && H < 65536 && W < 65536 && (long long)H * W < (1LL << 31) / 4,
+                 "egpt_raster: bad canvas capacity %dx%d", H, W);
   EGPT_CHECK_ARG(mode == EGPT_RASTER_LAST_WINS || mode == EGPT_RASTER_NEG_WINS, "egpt_raster: unknown mode %d", mode);
   EGPT_CHECK_ARG(dtype_size(x_dtype) && dtype_size(y_dtype) && dtype_size(p_dtype), "egpt_raster: unknown dtype");
   EGPT_CHECK_ARG(out_counts == nullptr || mode == EGPT_RASTER_LAST_WINS, "egpt_raster: counts only in LAST_WINS mode");
-  if (workspace_bytes < egpt_raster_workspace_bytes(n_windows, n_frames, H, W)) {
+  EGPT_CHECK_ARG(((uintptr_t)out_frames & 15) == 0 && ((uintptr_t)workspace & 15) == 0,
+                 "egpt_raster: out_frames and workspace must be 16-byte aligned");
+  const long long F = (long long)n_windows * n_frames;
+  EGPT_CHECK_ARG(F <= 65535, "egpt_raster: more than 65535 frames in one call");
+  RasterArgs a;
+  if (!make_tile_plan(H, W, F, &a.plan)) {
+    set_error("egpt_raster: a %d-pixel-wide sensor does not fit the shared-memory band (16 rows x W <= %d bytes)", W, kMaxPlaneBytes);
+    return EGPT_ERR_UNSUPPORTED;
+  }
+  const size_t per_range = (size_t)F * a.plan.plane_words * sizeof(uint32_t);
+  if (shrink_to_fit && (size_t)a.plan.K * per_range > workspace_bytes) a.plan.K = (int)(workspace_bytes / per_range);
+  if (a.plan.K < 1 || (size_t)a.plan.K * per_range > workspace_bytes) {
     set_error("egpt_raster: workspace %zu < %zu bytes", workspace_bytes, egpt_raster_workspace_bytes(n_windows, n_frames, H, W));
     return EGPT_ERR_WORKSPACE;
   }
-  const int F = n_windows * n_frames;
+  const long long items = F * a.plan.R * a.plan.K;
   const size_t frame_stride = egpt_raster_frame_stride(H, W);
   // algorithmic bytes are data dependent (5 B/event + 3 B/pixel written); the caller of
   // egpt_profile_collect supplies them, so only time is recorded here
   ProfScope prof(PROF_RASTER, 0.0, stream);
-  uint32_t* planes = (uint32_t*)workspace;
+  a.x = x; a.y = y; a.p = p; a.xdt = x_dtype; a.ydt = y_dtype; a.pdt = p_dtype;
+  a.offsets = window_offsets; a.n_frames = n_frames; a.H = H; a.W = W; a.fixed_canvas = fixed_canvas;
+  a.scratch = (uint32_t*)workspace; a.out_hw = out_hw; a.out_counts = out_counts; a.status = status;
   const bool fast = x_dtype == EGPT_U16 && y_dtype == EGPT_U16 && p_dtype == EGPT_U8 &&
                     ((uintptr_t)x % 16 == 0) && ((uintptr_t)y % 16 == 0) && ((uintptr_t)p % 8 == 0);
 
   if (fixed_canvas) {
-    set_fixed_hw_kernel<<<(F + 255) / 256, 256, 0, stream>>>(out_hw, F, H, W);
+    set_fixed_hw_kernel<<<(unsigned)((F + 255) / 256), 256, 0, stream>>>(out_hw, (int)F, H, W);
     EGPT_LAUNCH_CHECK();
   } else {
     EGPT_CUDA(cudaMemsetAsync(out_hw, 0, sizeof(int32_t) * 2 * F, stream));
   }
   if (out_counts) EGPT_CUDA(cudaMemsetAsync(out_counts, 0, sizeof(int32_t) * 2 * (size_t)F * H * W, stream));
 
-  const int cw = raster_chunk_windows(n_windows, n_frames, H, W);
-  for (int w0 = 0; w0 < n_windows; w0 += cw) {
-    const int nw = (w0 + cw <= n_windows) ? cw : n_windows - w0;
-    const int slices = nw * n_frames;
-    EGPT_CUDA(cudaMemsetAsync(planes, 0, (size_t)slices * H * W * sizeof(uint32_t), stream));
-    // enough CTAs per slice to fill the machine a few times over
-    int per_slice = (kNumSMs * 8 + slices - 1) / slices;
-    if (per_slice < 1) per_slice = 1;
-    if (per_slice > 64) per_slice = 64;
-    dim3 grid(per_slice, slices);
-    if (fast)
-      raster_scatter_kernel<true><<<grid, kScatterThreads, 0, stream>>>(x, y, p, x_dtype, y_dtype, p_dtype, window_offsets,
-          w0, n_frames, mode, H, W, fixed_canvas, planes, out_hw, out_counts, status);
-    else
-      raster_scatter_kernel<false><<<grid, kScatterThreads, 0, stream>>>(x, y, p, x_dtype, y_dtype, p_dtype, window_offsets,
-          w0, n_frames, mode, H, W, fixed_canvas, planes, out_hw, out_counts, status);
-    EGPT_LAUNCH_CHECK();
-    int cgrid = (int)(((size_t)H * W / 16 + 255) / 256);
-    if (cgrid > 64) cgrid = 64;
-    if (cgrid < 1) cgrid = 1;
-    raster_colourise_kernel<<<dim3(cgrid, slices), 256, 0, stream>>>(planes, out_hw, w0 * n_frames, H, W, out_frames, frame_stride);
-    EGPT_LAUNCH_CHECK();
+  if (mode == EGPT_RASTER_LAST_WINS) {
+    if (fast) EGPT_TRY((launch_tiles<true, EGPT_RASTER_LAST_WINS>(a, items, stream)));
+    else EGPT_TRY((launch_tiles<false, EGPT_RASTER_LAST_WINS>(a, items, stream)));
+  } else {
+    if (fast) EGPT_TRY((launch_tiles<true, EGPT_RASTER_NEG_WINS>(a, items, stream)));
+    else EGPT_TRY((launch_tiles<false, EGPT_RASTER_NEG_WINS>(a, items, stream)));
   }
+  int cgrid = (int)(((size_t)H * W / 16 + 255) / 256);
+  const int want = (int)((kNumSMs * 8 + F - 1) / F);
+  if (cgrid > want) cgrid = want;
+  if (cgrid < 1) cgrid = 1;
+  raster_colourise_kernel<<<dim3(cgrid, (unsigned)F), 256, 0, stream>>>(a.scratch, out_hw, window_offsets, n_frames, a.plan.K,
+                                                                        a.plan.plane_words, W, out_frames, frame_stride);
+  EGPT_LAUNCH_CHECK();
   return EGPT_OK;
+}
+}  // namespace egpt
+
+extern "C" int egpt_raster(const void* x, const void* y, const void* p, int x_dtype, int y_dtype, int p_dtype,
+                           const int64_t* window_offsets, int n_windows, int n_frames, int mode, int H, int W,
+                           int fixed_canvas, uint8_t* out_frames, int32_t* out_hw, int32_t* out_counts,
+                           int32_t* status, void* workspace, size_t workspace_bytes, void* stream) {
+  return raster_impl(x, y, p, x_dtype, y_dtype, p_dtype, window_offsets, n_windows, n_frames, mode, H, W, fixed_canvas,
+                     out_frames, out_hw, out_counts, status, workspace, workspace_bytes, false, (cudaStream_t)stream);
 }
 
 extern "C" size_t egpt_split_time_workspace_bytes(int64_t n_events, int max_windows) {
@@ -520,14 +716,14 @@ extern "C" int egpt_split_time(const void* x, const void* y, const void* t, cons
 // ------------------------------------------------------------------------------------------
 // egpt_raster_static: rasterisation for callers that cannot allocate device memory.
 // ------------------------------------------------------------------------------------------
-// Same result as egpt_raster, but the key planes live in a fixed array that is part of the
-// library image instead of a caller-supplied workspace.  Capacity: kStaticMaxKeys keys
-// (n_windows * n_frames * H * W), i.e. one 5-frame window of a 1280x720 sensor, or three
-// 5-frame windows of a 640x480 one.  Every GPU that loads the library carries these 17.6 MiB
-// until the process exits.
+// Same result as egpt_raster, but the partial planes (2 bits per pixel per event range) live in a
+// fixed array that is part of the library image instead of a caller-supplied workspace.
+// Capacity: n_windows * n_frames * H * W <= kStaticMaxKeys pixel cells, i.e. one 5-frame window of a
+// 1280x720 sensor, or three 5-frame windows of a 640x480 one.  Every GPU that loads the library
+// carries these 17.6 MiB until the process exits.
 namespace egpt {
 constexpr long long kStaticMaxKeys = 5LL * 720 * 1280;
-constexpr long long kStaticSlackWords = 1024;   // egpt_raster rounds its workspace need up by < 2 KiB
+constexpr long long kStaticSlackWords = 1024;
 static __device__ __align__(256) uint32_t g_static_key_planes[kStaticMaxKeys + kStaticSlackWords];
 
 // The array's name is only a handle on the host; the device address has to be asked for, once per
@@ -561,16 +757,18 @@ extern "C" int egpt_raster_static(const void* x, const void* y, const void* p, i
                                   void* stream) {
   EGPT_CHECK_ARG(n_windows > 0 && n_frames > 0 && H > 0 && W > 0, "egpt_raster_static: bad shape %d x %d x %d x %d",
                  n_windows, n_frames, H, W);
-  const long long keys = (long long)n_windows * n_frames * H * W;
-  if (keys > kStaticMaxKeys) {
-    set_error("egpt_raster_static: %d windows x %d frames x %dx%d needs %lld key cells, the built-in scratch holds %lld "
-              "(use egpt_raster with a caller workspace for larger requests)", n_windows, n_frames, H, W, keys, kStaticMaxKeys);
+  // compare by division: the product of four ints may not fit 64 bits
+  const long long frames = (long long)n_windows * n_frames, pixels = (long long)H * W;
+  if (frames > kStaticMaxKeys || pixels > kStaticMaxKeys / frames) {
+    set_error("egpt_raster_static: %d windows x %d frames x %dx%d exceeds the %lld pixel cells of the built-in scratch "
+              "(use egpt_raster with a caller workspace for larger requests)", n_windows, n_frames, H, W, kStaticMaxKeys);
     return EGPT_ERR_TOO_LARGE;
   }
   void* scratch = nullptr;
   EGPT_TRY(static_scratch_address(&scratch));
-  // egpt_raster zeroes the planes it is about to use, so whatever the previous call left behind is harmless
-  return egpt_raster(x, y, p, x_dtype, y_dtype, p_dtype, window_offsets, n_windows, n_frames, mode, H, W, fixed_canvas,
+  // every partial plane that is read is written in full by its band CTAs first, so whatever the
+  // previous call left in the array is harmless; the number of event ranges shrinks to what fits
+  return raster_impl(x, y, p, x_dtype, y_dtype, p_dtype, window_offsets, n_windows, n_frames, mode, H, W, fixed_canvas,
                      out_frames, out_hw, nullptr, status, scratch,
-                     (size_t)(kStaticMaxKeys + kStaticSlackWords) * sizeof(uint32_t), stream);
+                     (size_t)(kStaticMaxKeys + kStaticSlackWords) * sizeof(uint32_t), true, (cudaStream_t)stream);
 }
