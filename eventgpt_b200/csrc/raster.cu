@@ -103,50 +103,57 @@ struct RasterArgs {
   int32_t* status;
 };
 
-// eight consecutive events as loaded: x, y as 8 x u16, p as 8 x u8, and which of the eight belong to the slice
+// eight consecutive events as loaded: x, y as 8 x u16, p as 8 x u8.  An event that is not part of the slice (or lies
+// outside the sensor) is stored as y = 0xffff, which no band accepts.
 struct EventGroup {
   uint4 x, y;
   uint2 p;
-  unsigned valid;
+};
+
+struct ScanState {
+  unsigned px, py;          // packed u16x2 running maxima of the raw coordinates of whole groups
+  unsigned mx, my;          // running maxima of the coordinates of element-loaded groups
+  unsigned flags;
+  unsigned whole;           // bit g: group g of the batch came straight from memory (not yet range-checked)
 };
 
 template <bool FAST>
-__device__ __forceinline__ EventGroup load_group(const RasterArgs& a, long long g, long long g_end, const SliceInfo& sl,
-                                                 unsigned& flags) {
-  EventGroup e;
-  e.x = make_uint4(0, 0, 0, 0); e.y = make_uint4(0, 0, 0, 0); e.p = make_uint2(0, 0);
-  e.valid = 0;
-  if (g >= g_end) return e;
+__device__ __forceinline__ void load_group(const RasterArgs& a, long long g, long long g_end, const SliceInfo& sl,
+                                           EventGroup& e, ScanState& st, int slot) {
   const long long base = g << 3;
-  if (FAST && base >= sl.start && base + 8 <= sl.end) {
+  st.whole &= ~(1u << slot);
+  if (FAST && g < g_end && base >= sl.start && base + 8 <= sl.end) {
     e.x = __ldg(reinterpret_cast<const uint4*>(a.x) + g);
     e.y = __ldg(reinterpret_cast<const uint4*>(a.y) + g);
     e.p = __ldg(reinterpret_cast<const uint2*>(a.p) + g);
-    e.valid = 0xffu;
-    return e;
+    st.whole |= 1u << slot;
+    return;
   }
-  // slice boundary or generic element types: element loads, never outside [start, end)
-  unsigned xw[4] = {0, 0, 0, 0}, yw[4] = {0, 0, 0, 0}, pw[2] = {0, 0};
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const long long i = base + j;
-    if (i < sl.start || i >= sl.end) continue;
-    long long xl, yl, pl;
-    if (FAST) {
-      xl = ((const uint16_t*)a.x)[i]; yl = ((const uint16_t*)a.y)[i]; pl = ((const uint8_t*)a.p)[i];
-    } else {
-      xl = load_int(a.x, a.xdt, i); yl = load_int(a.y, a.ydt, i); pl = load_int(a.p, a.pdt, i);
+  // slice boundary (rare) or generic element types: element loads, never outside [start, end); range-checked here
+  unsigned long long xlo = 0, xhi = 0, ylo = ~0ull, yhi = ~0ull, pq = 0;
+  if (g < g_end) {
+#pragma unroll 1
+    for (int j = 0; j < 8; ++j) {
+      const long long i = base + j;
+      if (i < sl.start || i >= sl.end) continue;
+      long long xl, yl, pl;
+      if (FAST) {
+        xl = ((const uint16_t*)a.x)[i]; yl = ((const uint16_t*)a.y)[i]; pl = ((const uint8_t*)a.p)[i];
+      } else {
+        xl = load_int(a.x, a.xdt, i); yl = load_int(a.y, a.ydt, i); pl = load_int(a.p, a.pdt, i);
+      }
+      if (xl < 0 || yl < 0 || xl >= a.W || yl >= a.H) { st.flags |= EGPT_FLAG_OUT_OF_RANGE; continue; }
+      const int sh = (j & 3) * 16;
+      if (j < 4) { xlo |= (unsigned long long)xl << sh; ylo = (ylo & ~(0xffffull << sh)) | ((unsigned long long)yl << sh); }
+      else { xhi |= (unsigned long long)xl << sh; yhi = (yhi & ~(0xffffull << sh)) | ((unsigned long long)yl << sh); }
+      pq |= (unsigned long long)(pl == 0 ? 0u : (pl == 1 ? 1u : 2u)) << (j * 8);
+      st.mx = max(st.mx, (unsigned)xl);
+      st.my = max(st.my, (unsigned)yl);
     }
-    if (xl < 0 || yl < 0 || xl >= a.W || yl >= a.H) { flags |= EGPT_FLAG_OUT_OF_RANGE; continue; }
-    xw[j >> 1] |= (unsigned)xl << ((j & 1) * 16);
-    yw[j >> 1] |= (unsigned)yl << ((j & 1) * 16);
-    pw[j >> 2] |= (pl == 0 ? 0u : (pl == 1 ? 1u : 2u)) << ((j & 3) * 8);
-    e.valid |= 1u << j;
   }
-  e.x = make_uint4(xw[0], xw[1], xw[2], xw[3]);
-  e.y = make_uint4(yw[0], yw[1], yw[2], yw[3]);
-  e.p = make_uint2(pw[0], pw[1]);
-  return e;
+  e.x = make_uint4((unsigned)xlo, (unsigned)(xlo >> 32), (unsigned)xhi, (unsigned)(xhi >> 32));
+  e.y = make_uint4((unsigned)ylo, (unsigned)(ylo >> 32), (unsigned)yhi, (unsigned)(yhi >> 32));
+  e.p = make_uint2((unsigned)pq, (unsigned)(pq >> 32));
 }
 
 // 4 one-byte cells -> 4 two-bit codes: 0 untouched, 2 | (cell & 1) otherwise
@@ -154,6 +161,11 @@ __device__ __forceinline__ unsigned pack_cells4(unsigned w) {
   const unsigned nz = (((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w) & 0x80808080u;
   const unsigned c = (nz >> 6) | (w & 0x01010101u);
   return (c * 0x01041040u) >> 24;
+}
+
+// bytes != 0 -> 1, per byte
+__device__ __forceinline__ unsigned nonzero_bytes(unsigned w) {
+  return ((((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w) >> 7) & 0x01010101u;
 }
 
 // One CTA per (frame, band of rows, event range).  MODE 0: last event wins; MODE 1: negative wins.
@@ -178,16 +190,14 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
   const long long g_begin = g0 + ng * range / n_ranges, g_end = g0 + ng * (range + 1) / n_ranges;
   const unsigned y0 = (unsigned)band * a.plan.band_rows;
   const unsigned bh = min((unsigned)a.plan.band_rows, (unsigned)H - y0);
-  int32_t* counts = a.out_counts ? a.out_counts + (size_t)frame * 2 * H * W : nullptr;
 
   for (unsigned i = tid; i < a.plan.plane_smem / 16; i += kTileThreads) reinterpret_cast<uint4*>(plane)[i] = make_uint4(0, 0, 0, 0);
 
-  unsigned mx = 0, my = 0, flags = 0;
-  bool any = false;
+  ScanState st = {0, 0, 0, 0, 0, 0};
   EventGroup ev[kGroupsPerBatch];
 #pragma unroll
   for (int g = 0; g < kGroupsPerBatch; ++g)
-    ev[g] = load_group<FAST>(a, g_begin + (long long)(g * kTileWarps + warp) * 32 + lane, g_end, sl, flags);
+    load_group<FAST>(a, g_begin + (long long)(g * kTileWarps + warp) * 32 + lane, g_end, sl, ev[g], st, g);
   __syncthreads();
 
   for (long long gb = g_begin; gb < g_end; gb += kBatchGroups) {
@@ -198,36 +208,44 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
       const unsigned rank2 = (unsigned)(g * kTileWarps + warp + 1) << 1;
       const unsigned xw[4] = {ev[g].x.x, ev[g].x.y, ev[g].x.z, ev[g].x.w};
       const unsigned yw[4] = {ev[g].y.x, ev[g].y.y, ev[g].y.z, ev[g].y.w};
-      const unsigned pw[2] = {ev[g].p.x, ev[g].p.y};
+      if ((st.whole >> g) & 1u) {               // whole group straight from memory: its coordinates count for the
+        st.px = __vmaxu2(__vmaxu2(st.px, xw[0]), __vmaxu2(xw[1], __vmaxu2(xw[2], xw[3])));   // canvas and are range-checked
+        st.py = __vmaxu2(__vmaxu2(st.py, yw[0]), __vmaxu2(yw[1], __vmaxu2(yw[2], yw[3])));   // once, at the end
+      }
+      unsigned pw[2];
+      if (MODE == EGPT_RASTER_LAST_WINS) { pw[0] = nonzero_bytes(ev[g].p.x); pw[1] = nonzero_bytes(ev[g].p.y); }
+      else { pw[0] = ev[g].p.x; pw[1] = ev[g].p.y; }
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const unsigned xv = (xw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-        const unsigned yv = (yw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-        const unsigned pb = (pw[j >> 2] >> ((j & 3) * 8)) & 0xffu;
-        cell[g][j] = kNoCell;
-        if (!((ev[g].valid >> j) & 1u)) continue;
-        if (xv >= (unsigned)W || yv >= (unsigned)H) { flags |= EGPT_FLAG_OUT_OF_RANGE; continue; }
+        const unsigned xv = (j & 1) ? xw[j >> 1] >> 16 : xw[j >> 1] & 0xffffu;
+        const unsigned yv = (j & 1) ? yw[j >> 1] >> 16 : yw[j >> 1] & 0xffffu;
+        const unsigned pb = __byte_perm(pw[j >> 2], 0, 0x4440 | (j & 3));
         const unsigned yy = yv - y0;
-        if (yy >= bh) continue;                                    // another band's event
-        any = true;
-        mx = max(mx, xv); my = max(my, yv);
+        const bool ok = yy < bh && xv < (unsigned)W;               // in this band (y = 0xffff: not an event)
         const unsigned pix = yy * (unsigned)W + xv;
         if (MODE == EGPT_RASTER_LAST_WINS) {
-          const unsigned pol = pb != 0;
-          plane[pix] = (uint8_t)(rank2 | pol);
-          cell[g][j] = (pix << 1) | pol;
-          if (counts) atomicAdd(counts + (size_t)pol * H * W + (size_t)yv * W + xv, 1);
-        } else if (pb <= 1) {                                      // p == 0: negative (wins), p == 1: positive
+          if (ok) plane[pix] = (uint8_t)(rank2 | pb);
+          cell[g][j] = ok ? (pix << 1) | pb : kNoCell;
+        } else {                                                   // p == 0: negative (wins), p == 1: positive
+          const bool use = ok && pb <= 1;
           const unsigned val = pb ? 0x01u : 0xfeu;
-          if (plane[pix] < val) plane[pix] = (uint8_t)val;
-          cell[g][j] = (pix << 1) | pb;
+          if (use && plane[pix] < val) plane[pix] = (uint8_t)val;
+          cell[g][j] = use ? (pix << 1) | pb : kNoCell;
         }
       }
+    }
+    if (a.out_counts) {                                            // auxiliary per-pixel counts (no reference counterpart)
+      int32_t* counts = a.out_counts + (size_t)frame * 2 * H * W + (size_t)y0 * W;
+#pragma unroll
+      for (int g = 0; g < kGroupsPerBatch; ++g)
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (cell[g][j] != kNoCell) atomicAdd(counts + (size_t)(cell[g][j] & 1u) * H * W + (cell[g][j] >> 1), 1);
     }
     // the next batch's events travel while this one is checked
 #pragma unroll
     for (int g = 0; g < kGroupsPerBatch; ++g)
-      ev[g] = load_group<FAST>(a, gb + kBatchGroups + (long long)(g * kTileWarps + warp) * 32 + lane, g_end, sl, flags);
+      load_group<FAST>(a, gb + kBatchGroups + (long long)(g * kTileWarps + warp) * 32 + lane, g_end, sl, ev[g], st, g);
     __syncthreads();
 
     // ---- check: does every cell hold the latest event of the batch on its pixel? --------------------------
@@ -237,14 +255,13 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
       const unsigned rank2 = (unsigned)(g * kTileWarps + warp + 1) << 1;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        if (cell[g][j] == kNoCell) continue;
-        const unsigned c = plane[cell[g][j] >> 1];
-        if (MODE == EGPT_RASTER_LAST_WINS) {
-          const unsigned val = rank2 | (cell[g][j] & 1u);
-          if (c != val && c <= (rank2 | 1u)) bad |= 1u << (g * 8 + j);
-        } else {
-          if (c < ((cell[g][j] & 1u) ? 0x01u : 0xfeu)) bad |= 1u << (g * 8 + j);
-        }
+        const bool ok = cell[g][j] != kNoCell;
+        unsigned c = 0xffu;
+        if (ok) c = plane[cell[g][j] >> 1];
+        bool wrong;
+        if (MODE == EGPT_RASTER_LAST_WINS) wrong = c != (rank2 | (cell[g][j] & 1u)) && c <= (rank2 | 1u);
+        else wrong = c < ((cell[g][j] & 1u) ? 0x01u : 0xfeu);
+        bad |= (unsigned)wrong << (g * 8 + j);
       }
     }
     while (__syncthreads_or(bad != 0)) {
@@ -263,15 +280,13 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
             for (int j = 7; j >= 0; --j) if ((gm >> j) & 1u) mine = cell[g][j] >> 1;
             const unsigned P = __shfl_sync(0xffffffffu, mine, __ffs(ballot) - 1);
             int best = -1;
+            unsigned pol = 0;
 #pragma unroll
             for (int j = 0; j < 8; ++j)
-              if (cell[g][j] != kNoCell && (cell[g][j] >> 1) == P) { best = j; gm &= ~(1u << j); }
+              if (cell[g][j] != kNoCell && (cell[g][j] >> 1) == P) { best = j; pol = cell[g][j] & 1u; gm &= ~(1u << j); }
             const int key = best >= 0 ? lane * 8 + best : -1;
             const int top = __reduce_max_sync(0xffffffffu, key);
             if (best >= 0 && key == top) {
-              unsigned pol = 0;
-#pragma unroll
-              for (int j = 0; j < 8; ++j) if (j == best) pol = cell[g][j] & 1u;
               if (plane[P] <= (rank2 | 1u)) plane[P] = (uint8_t)(rank2 | pol);
               recheck |= 1u << (g * 8 + best);
             }
@@ -298,12 +313,10 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
           for (int j = 0; j < 8; ++j) {
             if (!((recheck >> (g * 8 + j)) & 1u)) continue;
             const unsigned c = plane[cell[g][j] >> 1];
-            if (MODE == EGPT_RASTER_LAST_WINS) {
-              const unsigned val = rank2 | (cell[g][j] & 1u);
-              if (c != val && c <= (rank2 | 1u)) bad |= 1u << (g * 8 + j);
-            } else {
-              if (c < ((cell[g][j] & 1u) ? 0x01u : 0xfeu)) bad |= 1u << (g * 8 + j);
-            }
+            bool wrong;
+            if (MODE == EGPT_RASTER_LAST_WINS) wrong = c != (rank2 | (cell[g][j] & 1u)) && c <= (rank2 | 1u);
+            else wrong = c < ((cell[g][j] & 1u) ? 0x01u : 0xfeu);
+            bad |= (unsigned)wrong << (g * 8 + j);
           }
         }
       }
@@ -320,17 +333,21 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
     }
   }
 
-  // canvas extent = (max y + 1, max x + 1) of the slice (common/common.py:65)
+  // whole groups are range-checked here, through their running maxima
+  unsigned mx = max(st.px & 0xffffu, st.px >> 16), my = max(st.py & 0xffffu, st.py >> 16);
+  if (mx >= (unsigned)W || my >= (unsigned)H) st.flags |= EGPT_FLAG_OUT_OF_RANGE;
+  mx = min(max(mx, st.mx), (unsigned)W - 1);
+  my = min(max(my, st.my), (unsigned)H - 1);
+  // canvas extent = (max y + 1, max x + 1) of the slice (common/common.py:65); a non-empty range holds an event
+  // (or the out-of-range flag is up, and the frame is not used)
   if (!a.fixed_canvas) {
-    unsigned vx = any ? mx + 1 : 0, vy = any ? my + 1 : 0;
-    vx = __reduce_max_sync(0xffffffffu, vx);
-    vy = __reduce_max_sync(0xffffffffu, vy);
-    if (lane == 0 && vx) {
-      atomicMax(a.out_hw + 2 * frame + 0, (int)vy);
-      atomicMax(a.out_hw + 2 * frame + 1, (int)vx);
+    const unsigned vx = __reduce_max_sync(0xffffffffu, mx), vy = __reduce_max_sync(0xffffffffu, my);
+    if (lane == 0) {
+      atomicMax(a.out_hw + 2 * frame + 0, (int)vy + 1);
+      atomicMax(a.out_hw + 2 * frame + 1, (int)vx + 1);
     }
   }
-  flags = __reduce_or_sync(0xffffffffu, flags);
+  const unsigned flags = __reduce_or_sync(0xffffffffu, st.flags);
   if (lane == 0 && flags) atomicOr(a.status, (int)flags);
 }
 
@@ -596,7 +613,7 @@ static int raster_impl(const void* x, const void* y, const void* p, int x_dtype,
   EGPT_CHECK_ARG(x && y && p && window_offsets && out_frames && out_hw && status && workspace,
                  "egpt_raster: null pointer argument");
   EGPT_CHECK_ARG(n_windows > 0 && n_frames > 0, "egpt_raster: n_windows=%d n_frames=%d must be positive", n_windows, n_frames);
-  EGPT_CHECK_ARG(H > 0 && W > 0 && H < 65536 && W < 65536 && (long long)H * W < (1LL << 31) / 4,
+  EGPT_CHECK_ARG(H > 0 && W > 0 && H < 65535 && W < 65535 && (long long)H * W < (1LL << 31) / 4,
                  "egpt_raster: bad canvas capacity %dx%d", H, W);
   EGPT_CHECK_ARG(mode == EGPT_RASTER_LAST_WINS || mode == EGPT_RASTER_NEG_WINS, "egpt_raster: unknown mode %d", mode);
   EGPT_CHECK_ARG(dtype_size(x_dtype) && dtype_size(y_dtype) && dtype_size(p_dtype), "egpt_raster: unknown dtype");
