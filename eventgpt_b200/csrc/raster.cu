@@ -37,7 +37,6 @@ constexpr int kBatchGroups = kTileThreads * kGroupsPerBatch;    // 2048 groups =
 constexpr int kMaxPlaneBytes = 200 * 1024;                      // band plane held in shared memory
 constexpr int kMaxRanges = 12;                                  // K: event ranges per slice
 constexpr long long kMinRangeGroups = 4096;                     // a range is at least 32 768 events
-constexpr unsigned kNoCell = 0xffffffffu;
 
 struct SliceInfo {
   long long start, end;
@@ -163,6 +162,16 @@ __device__ __forceinline__ unsigned pack_cells4(unsigned w) {
   return (c * 0x01041040u) >> 24;
 }
 
+// one-byte shared-memory accesses at a 32-bit shared address (keeps the address arithmetic out of the unrolled loops)
+__device__ __forceinline__ void sts_u8(unsigned addr, unsigned v) {
+  asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned lds_u8(unsigned addr) {
+  unsigned v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+
 // bytes != 0 -> 1, per byte
 __device__ __forceinline__ unsigned nonzero_bytes(unsigned w) {
   return ((((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w) >> 7) & 0x01010101u;
@@ -200,9 +209,14 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
     load_group<FAST>(a, g_begin + (long long)(g * kTileWarps + warp) * 32 + lane, g_end, sl, ev[g], st, g);
   __syncthreads();
 
+  unsigned plane_s = (unsigned)__cvta_generic_to_shared(plane);
+  asm volatile("mov.u32 %0, %0;" : "+r"(plane_s));          // opaque: kept in a register, not recomputed per access
+  const unsigned limit = bh * (unsigned)W;                  // cells of this band; a larger index is not this band's event
+  const unsigned band_off = y0 * (unsigned)W;
   for (long long gb = g_begin; gb < g_end; gb += kBatchGroups) {
     // ---- store: cell = rank of the 256-event chunk within the batch, and the polarity ------------------
-    unsigned cell[kGroupsPerBatch][8];          // (pixel << 1) | polarity bit, or kNoCell
+    unsigned pix[kGroupsPerBatch][8];           // cell index within the band (>= limit: none)
+    unsigned valw[kGroupsPerBatch][2];          // the eight cell values of a group, one byte each
 #pragma unroll
     for (int g = 0; g < kGroupsPerBatch; ++g) {
       const unsigned rank2 = (unsigned)(g * kTileWarps + warp + 1) << 1;
@@ -212,35 +226,42 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
         st.px = __vmaxu2(__vmaxu2(st.px, xw[0]), __vmaxu2(xw[1], __vmaxu2(xw[2], xw[3])));   // canvas and are range-checked
         st.py = __vmaxu2(__vmaxu2(st.py, yw[0]), __vmaxu2(yw[1], __vmaxu2(yw[2], yw[3])));   // once, at the end
       }
-      unsigned pw[2];
-      if (MODE == EGPT_RASTER_LAST_WINS) { pw[0] = nonzero_bytes(ev[g].p.x); pw[1] = nonzero_bytes(ev[g].p.y); }
-      else { pw[0] = ev[g].p.x; pw[1] = ev[g].p.y; }
+      if (MODE == EGPT_RASTER_LAST_WINS) {
+        valw[g][0] = nonzero_bytes(ev[g].p.x) | (rank2 * 0x01010101u);
+        valw[g][1] = nonzero_bytes(ev[g].p.y) | (rank2 * 0x01010101u);
+      } else {                                  // p == 0: negative (0xfe, wins), p == 1: positive (0x01), other p: ignored (0)
+        valw[g][0] = (nonzero_bytes(ev[g].p.x) ^ 0x01010101u) * 0xfeu | (nonzero_bytes(ev[g].p.x ^ 0x01010101u) ^ 0x01010101u);
+        valw[g][1] = (nonzero_bytes(ev[g].p.y) ^ 0x01010101u) * 0xfeu | (nonzero_bytes(ev[g].p.y ^ 0x01010101u) ^ 0x01010101u);
+      }
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const unsigned xv = (j & 1) ? xw[j >> 1] >> 16 : xw[j >> 1] & 0xffffu;
         const unsigned yv = (j & 1) ? yw[j >> 1] >> 16 : yw[j >> 1] & 0xffffu;
-        const unsigned pb = __byte_perm(pw[j >> 2], 0, 0x4440 | (j & 3));
-        const unsigned yy = yv - y0;
-        const bool ok = yy < bh && xv < (unsigned)W;               // in this band (y = 0xffff: not an event)
-        const unsigned pix = yy * (unsigned)W + xv;
+        const unsigned val = __byte_perm(valw[g][j >> 2], 0, 0x4440 | (j & 3));
+        // rows below the band wrap to a huge index, rows above it (and y = 0xffff: not an event) exceed the limit; an x
+        // beyond the sensor can land on a wrong pixel of the band, but never outside it (the call then reports
+        // EGPT_FLAG_OUT_OF_RANGE and the frames are not used)
+        const unsigned q = yv * (unsigned)W + xv - band_off;
+        pix[g][j] = q;
         if (MODE == EGPT_RASTER_LAST_WINS) {
-          if (ok) plane[pix] = (uint8_t)(rank2 | pb);
-          cell[g][j] = ok ? (pix << 1) | pb : kNoCell;
-        } else {                                                   // p == 0: negative (wins), p == 1: positive
-          const bool use = ok && pb <= 1;
-          const unsigned val = pb ? 0x01u : 0xfeu;
-          if (use && plane[pix] < val) plane[pix] = (uint8_t)val;
-          cell[g][j] = use ? (pix << 1) | pb : kNoCell;
+          if (q < limit) sts_u8(plane_s + q, val);
+        } else {
+          if (q < limit && lds_u8(plane_s + q) < val) sts_u8(plane_s + q, val);
         }
       }
     }
     if (a.out_counts) {                                            // auxiliary per-pixel counts (no reference counterpart)
-      int32_t* counts = a.out_counts + (size_t)frame * 2 * H * W + (size_t)y0 * W;
-#pragma unroll
+      int32_t* counts = a.out_counts + (size_t)frame * 2 * H * W + band_off;
+#pragma unroll 1
       for (int g = 0; g < kGroupsPerBatch; ++g)
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (cell[g][j] != kNoCell) atomicAdd(counts + (size_t)(cell[g][j] & 1u) * H * W + (cell[g][j] >> 1), 1);
+        for (int j = 0; j < 8; ++j) {
+          unsigned q = 0, v = 0;
+#pragma unroll
+          for (int gg = 0; gg < kGroupsPerBatch; ++gg)
+            if (gg == g) { q = pix[gg][j]; v = __byte_perm(valw[gg][j >> 2], 0, 0x4440 | (j & 3)); }
+          if (q < limit) atomicAdd(counts + (size_t)(v & 1u) * H * W + q, 1);
+        }
     }
     // the next batch's events travel while this one is checked
 #pragma unroll
@@ -252,16 +273,14 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
     unsigned bad = 0;
 #pragma unroll
     for (int g = 0; g < kGroupsPerBatch; ++g) {
-      const unsigned rank2 = (unsigned)(g * kTileWarps + warp + 1) << 1;
+      const unsigned hi = ((unsigned)(g * kTileWarps + warp + 1) << 1) | 1u;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const bool ok = cell[g][j] != kNoCell;
+        const unsigned val = __byte_perm(valw[g][j >> 2], 0, 0x4440 | (j & 3));
         unsigned c = 0xffu;
-        if (ok) c = plane[cell[g][j] >> 1];
-        bool wrong;
-        if (MODE == EGPT_RASTER_LAST_WINS) wrong = c != (rank2 | (cell[g][j] & 1u)) && c <= (rank2 | 1u);
-        else wrong = c < ((cell[g][j] & 1u) ? 0x01u : 0xfeu);
-        bad |= (unsigned)wrong << (g * 8 + j);
+        if (pix[g][j] < limit) c = lds_u8(plane_s + pix[g][j]);
+        const bool wrong = MODE == EGPT_RASTER_LAST_WINS ? (c != val && c <= hi) : c < val;
+        if (wrong) bad |= 1u << (g * 8 + j);
       }
     }
     while (__syncthreads_or(bad != 0)) {
@@ -269,7 +288,7 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
       if (MODE == EGPT_RASTER_LAST_WINS) {
 #pragma unroll
         for (int g = 0; g < kGroupsPerBatch; ++g) {
-          const unsigned rank2 = (unsigned)(g * kTileWarps + warp + 1) << 1;
+          const unsigned hi = ((unsigned)(g * kTileWarps + warp + 1) << 1) | 1u;
           unsigned gm = (bad >> (g * 8)) & 0xffu;
           // one step per disputed pixel of this warp's chunk: the latest event of the chunk on it writes
           for (;;) {
@@ -277,17 +296,17 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
             if (!ballot) break;
             unsigned mine = 0;
 #pragma unroll
-            for (int j = 7; j >= 0; --j) if ((gm >> j) & 1u) mine = cell[g][j] >> 1;
+            for (int j = 7; j >= 0; --j) if ((gm >> j) & 1u) mine = pix[g][j];
             const unsigned P = __shfl_sync(0xffffffffu, mine, __ffs(ballot) - 1);
             int best = -1;
-            unsigned pol = 0;
+            unsigned val = 0;
 #pragma unroll
             for (int j = 0; j < 8; ++j)
-              if (cell[g][j] != kNoCell && (cell[g][j] >> 1) == P) { best = j; pol = cell[g][j] & 1u; gm &= ~(1u << j); }
+              if (pix[g][j] == P) { best = j; val = __byte_perm(valw[g][j >> 2], 0, 0x4440 | (j & 3)); gm &= ~(1u << j); }
             const int key = best >= 0 ? lane * 8 + best : -1;
             const int top = __reduce_max_sync(0xffffffffu, key);
             if (best >= 0 && key == top) {
-              if (plane[P] <= (rank2 | 1u)) plane[P] = (uint8_t)(rank2 | pol);
+              if (lds_u8(plane_s + P) <= hi) sts_u8(plane_s + P, val);
               recheck |= 1u << (g * 8 + best);
             }
           }
@@ -298,8 +317,8 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             if ((bad >> (g * 8 + j)) & 1u) {
-              const unsigned val = (cell[g][j] & 1u) ? 0x01u : 0xfeu;
-              if (plane[cell[g][j] >> 1] < val) plane[cell[g][j] >> 1] = (uint8_t)val;
+              const unsigned val = __byte_perm(valw[g][j >> 2], 0, 0x4440 | (j & 3));
+              if (lds_u8(plane_s + pix[g][j]) < val) sts_u8(plane_s + pix[g][j], val);
               recheck |= 1u << (g * 8 + j);
             }
       }
@@ -308,15 +327,14 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
       if (recheck) {
 #pragma unroll
         for (int g = 0; g < kGroupsPerBatch; ++g) {
-          const unsigned rank2 = (unsigned)(g * kTileWarps + warp + 1) << 1;
+          const unsigned hi = ((unsigned)(g * kTileWarps + warp + 1) << 1) | 1u;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             if (!((recheck >> (g * 8 + j)) & 1u)) continue;
-            const unsigned c = plane[cell[g][j] >> 1];
-            bool wrong;
-            if (MODE == EGPT_RASTER_LAST_WINS) wrong = c != (rank2 | (cell[g][j] & 1u)) && c <= (rank2 | 1u);
-            else wrong = c < ((cell[g][j] & 1u) ? 0x01u : 0xfeu);
-            bad |= (unsigned)wrong << (g * 8 + j);
+            const unsigned val = __byte_perm(valw[g][j >> 2], 0, 0x4440 | (j & 3));
+            const unsigned c = lds_u8(plane_s + pix[g][j]);
+            const bool wrong = MODE == EGPT_RASTER_LAST_WINS ? (c != val && c <= hi) : c < val;
+            if (wrong) bad |= 1u << (g * 8 + j);
           }
         }
       }
