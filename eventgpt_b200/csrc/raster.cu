@@ -172,6 +172,11 @@ __device__ __forceinline__ unsigned lds_u8(unsigned addr) {
   return v;
 }
 
+// byte j of the eight packed cell values of a group
+__device__ __forceinline__ unsigned cell_value(const unsigned (&vw)[2], int j) {
+  return __dp4a(vw[j >> 2], 1u << (8 * (j & 3)), 0u);
+}
+
 // bytes != 0 -> 1, per byte
 __device__ __forceinline__ unsigned nonzero_bytes(unsigned w) {
   return ((((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w) >> 7) & 0x01010101u;
@@ -182,7 +187,10 @@ template <bool FAST, int MODE>
 __global__ void __launch_bounds__(kTileThreads, 1)
 raster_tile_kernel(const __grid_constant__ RasterArgs a) {
   extern __shared__ __align__(16) uint8_t plane[];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31;
+  // chunk order within a batch: the warp scheduler favours high warp ids, so they take the EARLY chunks -- stores then tend
+  // to land in chunk order and few cells need the repair step (a matter of speed only)
+  const int wrank = kTileWarps - 1 - (tid >> 5);
   const int R = a.plan.R, K = a.plan.K, H = a.H, W = a.W;
   const long long item = blockIdx.x;
   const int band = (int)(item % R), range = (int)((item / R) % K);
@@ -206,7 +214,7 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
   EventGroup ev[kGroupsPerBatch];
 #pragma unroll
   for (int g = 0; g < kGroupsPerBatch; ++g)
-    load_group<FAST>(a, g_begin + (long long)(g * kTileWarps + warp) * 32 + lane, g_end, sl, ev[g], st, g);
+    load_group<FAST>(a, g_begin + (long long)(g * kTileWarps + wrank) * 32 + lane, g_end, sl, ev[g], st, g);
   __syncthreads();
 
   unsigned plane_s = (unsigned)__cvta_generic_to_shared(plane);
@@ -219,7 +227,7 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
     unsigned valw[kGroupsPerBatch][2];          // the eight cell values of a group, one byte each
 #pragma unroll
     for (int g = 0; g < kGroupsPerBatch; ++g) {
-      const unsigned rank2 = (unsigned)(g * kTileWarps + warp + 1) << 1;
+      const unsigned rank2 = (unsigned)(g * kTileWarps + wrank + 1) << 1;
       const unsigned xw[4] = {ev[g].x.x, ev[g].x.y, ev[g].x.z, ev[g].x.w};
       const unsigned yw[4] = {ev[g].y.x, ev[g].y.y, ev[g].y.z, ev[g].y.w};
       if ((st.whole >> g) & 1u) {               // whole group straight from memory: its coordinates count for the
@@ -235,13 +243,14 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
       }
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const unsigned xv = (j & 1) ? xw[j >> 1] >> 16 : xw[j >> 1] & 0xffffu;
-        const unsigned yv = (j & 1) ? yw[j >> 1] >> 16 : yw[j >> 1] & 0xffffu;
-        const unsigned val = __byte_perm(valw[g][j >> 2], 0, 0x4440 | (j & 3));
+        // field extraction on the multiply-add pipe (dot products with a one-hot selector): the integer-logic pipe is
+        // the busier one in this kernel
+        const unsigned yv = __dp2a_lo(yw[j >> 1], (j & 1) ? 0x0100u : 0x0001u, 0u);
+        const unsigned val = cell_value(valw[g], j);
         // rows below the band wrap to a huge index, rows above it (and y = 0xffff: not an event) exceed the limit; an x
         // beyond the sensor can land on a wrong pixel of the band, but never outside it (the call then reports
         // EGPT_FLAG_OUT_OF_RANGE and the frames are not used)
-        const unsigned q = yv * (unsigned)W + xv - band_off;
+        const unsigned q = __dp2a_lo(xw[j >> 1], (j & 1) ? 0x0100u : 0x0001u, yv * (unsigned)W - band_off);
         pix[g][j] = q;
         if (MODE == EGPT_RASTER_LAST_WINS) {
           if (q < limit) sts_u8(plane_s + q, val);
@@ -259,55 +268,68 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
           unsigned q = 0, v = 0;
 #pragma unroll
           for (int gg = 0; gg < kGroupsPerBatch; ++gg)
-            if (gg == g) { q = pix[gg][j]; v = __byte_perm(valw[gg][j >> 2], 0, 0x4440 | (j & 3)); }
+            if (gg == g) { q = pix[gg][j]; v = cell_value(valw[gg], j); }
           if (q < limit) atomicAdd(counts + (size_t)(v & 1u) * H * W + q, 1);
         }
     }
     // the next batch's events travel while this one is checked
 #pragma unroll
     for (int g = 0; g < kGroupsPerBatch; ++g)
-      load_group<FAST>(a, gb + kBatchGroups + (long long)(g * kTileWarps + warp) * 32 + lane, g_end, sl, ev[g], st, g);
+      load_group<FAST>(a, gb + kBatchGroups + (long long)(g * kTileWarps + wrank) * 32 + lane, g_end, sl, ev[g], st, g);
     __syncthreads();
 
     // ---- check: does every cell hold the latest event of the batch on its pixel? --------------------------
     unsigned bad = 0;
+    unsigned rq = 0, rv = 0, ridx = 0;          // the (last) event found wrong: cell address, value, index in the batch
 #pragma unroll
     for (int g = 0; g < kGroupsPerBatch; ++g) {
-      const unsigned hi = ((unsigned)(g * kTileWarps + warp + 1) << 1) | 1u;
+      const unsigned hi = ((unsigned)(g * kTileWarps + wrank + 1) << 1) | 1u;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const unsigned val = __byte_perm(valw[g][j >> 2], 0, 0x4440 | (j & 3));
+        const unsigned val = cell_value(valw[g], j);
         unsigned c = 0xffu;
         if (pix[g][j] < limit) c = lds_u8(plane_s + pix[g][j]);
         const bool wrong = MODE == EGPT_RASTER_LAST_WINS ? (c != val && c <= hi) : c < val;
-        if (wrong) bad |= 1u << (g * 8 + j);
+        if (wrong) { bad |= 1u << (g * 8 + j); rq = plane_s + pix[g][j]; rv = val; ridx = g * 8 + j; }
       }
     }
     while (__syncthreads_or(bad != 0)) {
       unsigned recheck = 0;
+      bool single = false;
       if (MODE == EGPT_RASTER_LAST_WINS) {
+        // the common dispute: ONE event of this thread found an earlier chunk's value in its cell (that store landed
+        // after ours).  The thread stores again, alone; everything else goes to the warp-wide step below.
+        const unsigned rhi = ((unsigned)((ridx >> 3) * kTileWarps + wrank + 1) << 1) | 1u;
+        unsigned coop = bad;
+        if (bad != 0 && bad == (1u << ridx)) {
+          const unsigned c = lds_u8(rq);
+          if (c > rhi || c == rv) { bad = 0; coop = 0; }                    // a later chunk (or our value) holds the pixel by now
+          else if (c < (rhi ^ 1u)) { sts_u8(rq, rv); single = true; coop = 0; }
+        }
+        if (__ballot_sync(0xffffffffu, coop != 0)) {
 #pragma unroll
-        for (int g = 0; g < kGroupsPerBatch; ++g) {
-          const unsigned hi = ((unsigned)(g * kTileWarps + warp + 1) << 1) | 1u;
-          unsigned gm = (bad >> (g * 8)) & 0xffu;
-          // one step per disputed pixel of this warp's chunk: the latest event of the chunk on it writes
-          for (;;) {
-            const unsigned ballot = __ballot_sync(0xffffffffu, gm != 0);
-            if (!ballot) break;
-            unsigned mine = 0;
+          for (int g = 0; g < kGroupsPerBatch; ++g) {
+            const unsigned hi = ((unsigned)(g * kTileWarps + wrank + 1) << 1) | 1u;
+            unsigned gm = (coop >> (g * 8)) & 0xffu;
+            // one step per disputed pixel of this warp's chunk: the latest event of the chunk on it writes
+            for (;;) {
+              const unsigned ballot = __ballot_sync(0xffffffffu, gm != 0);
+              if (!ballot) break;
+              unsigned mine = 0;
 #pragma unroll
-            for (int j = 7; j >= 0; --j) if ((gm >> j) & 1u) mine = pix[g][j];
-            const unsigned P = __shfl_sync(0xffffffffu, mine, __ffs(ballot) - 1);
-            int best = -1;
-            unsigned val = 0;
+              for (int j = 7; j >= 0; --j) if ((gm >> j) & 1u) mine = pix[g][j];
+              const unsigned P = __shfl_sync(0xffffffffu, mine, __ffs(ballot) - 1);
+              int best = -1;
+              unsigned val = 0;
 #pragma unroll
-            for (int j = 0; j < 8; ++j)
-              if (pix[g][j] == P) { best = j; val = __byte_perm(valw[g][j >> 2], 0, 0x4440 | (j & 3)); gm &= ~(1u << j); }
-            const int key = best >= 0 ? lane * 8 + best : -1;
-            const int top = __reduce_max_sync(0xffffffffu, key);
-            if (best >= 0 && key == top) {
-              if (lds_u8(plane_s + P) <= hi) sts_u8(plane_s + P, val);
-              recheck |= 1u << (g * 8 + best);
+              for (int j = 0; j < 8; ++j)
+                if (pix[g][j] == P) { best = j; val = cell_value(valw[g], j); gm &= ~(1u << j); }
+              const int key = best >= 0 ? lane * 8 + best : -1;
+              const int top = __reduce_max_sync(0xffffffffu, key);
+              if (best >= 0 && key == top) {
+                if (lds_u8(plane_s + P) <= hi) sts_u8(plane_s + P, val);
+                recheck |= 1u << (g * 8 + best);
+              }
             }
           }
         }
@@ -317,27 +339,33 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             if ((bad >> (g * 8 + j)) & 1u) {
-              const unsigned val = __byte_perm(valw[g][j >> 2], 0, 0x4440 | (j & 3));
+              const unsigned val = cell_value(valw[g], j);
               if (lds_u8(plane_s + pix[g][j]) < val) sts_u8(plane_s + pix[g][j], val);
               recheck |= 1u << (g * 8 + j);
             }
       }
       __syncthreads();
-      bad = 0;
+      unsigned still = 0;
+      if (single) {
+        const unsigned rhi = ((unsigned)((ridx >> 3) * kTileWarps + wrank + 1) << 1) | 1u;
+        const unsigned c = lds_u8(rq);
+        if (c != rv && c <= rhi) still = bad;
+      }
       if (recheck) {
 #pragma unroll
         for (int g = 0; g < kGroupsPerBatch; ++g) {
-          const unsigned hi = ((unsigned)(g * kTileWarps + warp + 1) << 1) | 1u;
+          const unsigned hi = ((unsigned)(g * kTileWarps + wrank + 1) << 1) | 1u;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             if (!((recheck >> (g * 8 + j)) & 1u)) continue;
-            const unsigned val = __byte_perm(valw[g][j >> 2], 0, 0x4440 | (j & 3));
+            const unsigned val = cell_value(valw[g], j);
             const unsigned c = lds_u8(plane_s + pix[g][j]);
             const bool wrong = MODE == EGPT_RASTER_LAST_WINS ? (c != val && c <= hi) : c < val;
-            if (wrong) bad |= 1u << (g * 8 + j);
+            if (wrong) still |= 1u << (g * 8 + j);
           }
         }
       }
+      bad = still;
     }
   }
 
