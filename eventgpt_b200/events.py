@@ -71,8 +71,8 @@ def to_device(arr, device):
 
 
 def check_status(status, what):
-    """Turns the device status word into the exceptions the reference raises."""
-    flags = int(status.item())
+    """Turns the device status word (a tensor, or its value already on the host) into the exceptions the reference raises."""
+    flags = int(status.item()) if isinstance(status, torch.Tensor) else int(status)
     if flags & _lib.FLAG_EMPTY_SLICE:
         # reference: y.max() on an empty slice -> ValueError (common/common.py:65)
         raise ValueError("zero-size array to reduction operation maximum which has no identity "

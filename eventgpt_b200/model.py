@@ -335,17 +335,21 @@ class EventGPTVisualFrontEnd:
         return llm.generate(**out) if llm is not None else out
 
     # ---- fused path: events -> tokens ------------------------------------------------------------
-    def visual_tokens(self, x, y, p, window_offsets, sensor_size, n_frames=E.N_FRAMES, out=None, check_flags=True):
+    def visual_tokens(self, x, y, p, window_offsets, sensor_size, n_frames=E.N_FRAMES, out=None, check_flags=True,
+                      status=None):
         """process_event_data (common/common.py:110-129) + the list branch (:326-343) for a batch of
         windows, device resident end to end.  x, y, p: device integer tensors holding all windows back
-        to back; window_offsets: int64 [B+1] on the device.  Returns tokens bf16 [B, n_frames+577, 4096]."""
+        to back; window_offsets: int64 [B+1] on the device.  Returns tokens bf16 [B, n_frames+577, 4096].
+        ``status`` (int32 [1] on the device, zeroed by the caller) receives the data-dependent flags when the caller
+        checks them later itself (``check_flags=False``: no host synchronisation here)."""
         dev = x.device
         H, W = int(sensor_size[0]), int(sensor_size[1])
         B = window_offsets.numel() - 1
         if out is None:
             out = torch.empty((B, n_frames + TOKENS, LLM), dtype=torch.bfloat16, device=dev)
         hw = torch.empty((B * n_frames, 2), dtype=torch.int32, device=dev)
-        status = torch.zeros(1, dtype=torch.int32, device=dev)
+        if status is None:
+            status = torch.zeros(1, dtype=torch.int32, device=dev)
         nws = lib().egpt_visual_tokens_workspace_bytes(B, n_frames, H, W)
         ws = E.Workspace.get(dev, "fused", nws)
         check(lib().egpt_visual_tokens(self._handle, E.ptr(x), E.ptr(y), E.ptr(p), E._CODE_OF_TORCH[x.dtype],

@@ -30,6 +30,11 @@ class VisualTokenStream:
         self.doff = [torch.empty(max_windows + 1, dtype=torch.int64, device=d) for _ in range(depth)]
         self.tok = [torch.empty((max_windows, n_frames + TOKENS, LLM), dtype=torch.bfloat16, device=d) for _ in range(depth)]
         self.htok = [torch.empty((max_windows, n_frames + TOKENS, LLM), dtype=torch.bfloat16).pin_memory() for _ in range(depth)]
+        # data-dependent flags of a batch (empty slice -> the reference's ValueError, coordinate out of range, ...): one
+        # device word per slot, copied out next to the tokens and turned into the exception in wait() / drain()
+        self.status = [torch.zeros(1, dtype=torch.int32, device=d) for _ in range(depth)]
+        self.hstatus = [torch.zeros(1, dtype=torch.int32).pin_memory() for _ in range(depth)]
+        self.unchecked = [False] * depth
         self.s_in, self.s_out = torch.cuda.Stream(d), torch.cuda.Stream(d)
         self.ev_h2d = [torch.cuda.Event() for _ in range(depth)]
         self.ev_done = [torch.cuda.Event() for _ in range(depth)]
@@ -63,19 +68,30 @@ class VisualTokenStream:
         if self.posted[s] is not None:
             self.posted[s].wait()                          # ... also by the slot's asynchronous post step
             self.posted[s] = None
+        if self.unchecked[s]:
+            self._check(s)                                 # nobody waited for the slot's previous batch: its flags are due now
+        self.status[s].zero_()
         self.fe.visual_tokens(self.dx[s][:n], self.dy[s][:n], self.dp[s][:n], self.doff[s][:B + 1], self.sensor,
-                              n_frames=self.n_frames, out=self.tok[s][:B], check_flags=False)
+                              n_frames=self.n_frames, out=self.tok[s][:B], check_flags=False, status=self.status[s])
         if post is not None:
             self.posted[s] = post(self.tok[s][:B], s)      # e.g. the final all_gather of a multi-GPU job
         self.ev_done[s].record(compute)
         self.s_out.wait_event(self.ev_done[s])
         with torch.cuda.stream(self.s_out):
             self.htok[s][:B].copy_(self.tok[s][:B], non_blocking=True)
+            self.hstatus[s].copy_(self.status[s], non_blocking=True)
             self.ev_d2h[s].record(self.s_out)
+        self.unchecked[s] = True
         return s
 
-    def wait(self, slot):
+    def _check(self, slot):
+        """Raises what the reference raises for the slot's last batch (ValueError for an empty slice, ...)."""
         self.ev_d2h[slot].synchronize()
+        self.unchecked[slot] = False
+        E.check_status(int(self.hstatus[slot][0]), f"VisualTokenStream slot {slot}")
+
+    def wait(self, slot):
+        self._check(slot)
         return self.htok[slot]
 
     def join(self):
@@ -94,3 +110,6 @@ class VisualTokenStream:
                 self.posted[s] = None
         self.s_out.synchronize()
         torch.cuda.current_stream(self.dev).synchronize()
+        for s in range(self.depth):
+            if self.unchecked[s]:
+                self._check(s)

@@ -287,6 +287,20 @@ def test_host_fed_stream_matches_direct_call(frontends, dev):
     for (hx, hy, hp, hoff), g in zip(batches, got):
         want = fe.visual_tokens(hx.to(dev), hy.to(dev), hp.to(dev), hoff.to(dev), (H, W)).cpu()
         assert torch.equal(g, want)
+    # a window with fewer events than frames has an empty slice: the reference raises ValueError from y.max()
+    # (common/common.py:65); the serving loop must deliver it for that batch -- in wait(), or at the latest when the
+    # slot is reused or drained -- and carry on with the next batch
+    hx, hy, hp, _ = batches[0]
+    bad_off = torch.tensor([0, 3, 2 * N], dtype=torch.int64).pin_memory()
+    s = vs.submit(hx, hy, hp, bad_off)
+    with pytest.raises(ValueError):
+        vs.wait(s)
+    vs.submit(hx, hy, hp, bad_off)
+    with pytest.raises(ValueError):
+        vs.drain()
+    s = vs.submit(*batches[1])
+    assert torch.equal(vs.wait(s)[:B], got[1])
+    vs.drain()
 
 
 def test_attention_lazy_rescale_and_peaked_rows(dev):
