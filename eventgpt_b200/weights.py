@@ -72,3 +72,29 @@ def random_state_dict(seed=0, num_layers=24):
             v = 0.02 * r
         sd[k] = v.to(torch.bfloat16).to(torch.float32)
     return sd
+
+
+OUTLIER_CHANNELS = (7, 300, 777, 1001)
+PEAKED = {3: (0, 5), 10: (2, 9), 17: (4, 15)}          # layer -> heads with sharpened attention
+
+
+def outlier_state_dict(seed=1, num_layers=24):
+    """``random_state_dict`` reshaped towards what a trained CLIP-L tower looks like numerically: a few residual
+    channels carry "massive activations" (every layer's fc2 bias pushes ``OUTLIER_CHANNELS`` further out, so that the
+    last hidden state holds them at ~50x the median channel), and a few heads have q/k projections scaled so that
+    their softmax rows are sharply peaked.  Used for a second 24-layer parity golden; every value stays
+    bf16-representable."""
+    sd = random_state_dict(seed, num_layers)
+    pos = sd[VT + "embeddings.position_embedding.weight"]
+    for i, ch in enumerate(OUTLIER_CHANNELS):
+        pos[:, ch] += (8.0 if i % 2 == 0 else -6.0)
+        for l in range(num_layers):
+            sd[f"{VT}encoder.layers.{l}.mlp.fc2.bias"][ch] += (10.0 if i % 2 == 0 else -8.0)
+    for l, heads in PEAKED.items():
+        if l >= num_layers:
+            continue
+        for n in ("q", "k"):
+            w = sd[f"{VT}encoder.layers.{l}.self_attn.{n}_proj.weight"]
+            for h in heads:
+                w[h * 64:(h + 1) * 64] *= 6.0
+    return {k: v.to(torch.bfloat16).to(torch.float32) for k, v in sd.items()}

@@ -184,6 +184,80 @@ def main():
         print(m)
 
 
+def synth_window(global_index, n_events=1_000_000, h=480, w=640):
+    """The benchmark's window generator (bench.py synth_window), restated so that the golden does not
+    depend on bench.py: dense uniform events with one event at the sensor corner in every slice."""
+    rng = np.random.default_rng([1, global_index])
+    x = rng.integers(0, w, n_events).astype(np.uint16)
+    y = rng.integers(0, h, n_events).astype(np.uint16)
+    p = rng.integers(0, 2, n_events).astype(np.uint8)
+    k = n_events // N_FRAMES
+    for i in range(N_FRAMES):
+        x[i * k] = w - 1
+        y[i * k] = h - 1
+    return x, y, p
+
+
+def make_full_token_goldens(only=None):
+    """24-layer tokens of the REAL reference model (fp32, CPU), FULL [582, 4096] tensors stored as float16 (quantisation
+    <= 2e-3 at |x| <= 4, stated in the tests), for: the reference's sample1, one DSEC window, one window of the benchmark
+    workload (dense 1M events), and sample1 again under weights with outlier channels and peaked attention heads.  Next to
+    each, the reference's own bf16 execution against its fp32 one (the yardstick of SURVEY F1)."""
+    from eventgpt_b200.weights import outlier_state_dict
+    C, M = ref_harness.import_reference()
+    proc = ref_harness.pil_processor()
+    dsec = load_npy(f"{REF}/feasible/egpt_dataset/event_npy/interlaken_00_d/000069.npy")
+    x, y, p = synth_window(0)
+    inputs = {
+        "sample1": load_npy(f"{REF}/samples/sample1.npy"),
+        "dsec_000069": dsec,
+        "dense1m": dict(x=x, y=y, p=p, t=np.zeros(len(x), np.int8)),
+    }
+    pix = {}
+    for name, ev in inputs.items():
+        ev = {k: np.asarray(ev[k]) for k in ("x", "y", "t", "p")}
+        if name == "dense1m":
+            from oracle import events as oev          # the reference loop takes ~2 s per 1M events; same frames (pinned)
+            frames = oev.get_event_images_list(ev, N_FRAMES)
+            chk = C.get_event_images_list({k: v[:50_000] for k, v in ev.items()}, N_FRAMES)
+            assert all(np.array_equal(a, b) for a, b in zip(chk, oev.get_event_images_list({k: v[:50_000] for k, v in ev.items()}, N_FRAMES)))
+        else:
+            frames = C.get_event_images_list(ev, N_FRAMES)
+        pix[name] = [proc(f, return_tensors="pt")["pixel_values"][0].to(torch.bfloat16) for f in frames]
+    jobs = [("sample1", "random", random_state_dict(0, 24)), ("dsec_000069", "random", None), ("dense1m", "random", None),
+            ("sample1", "outlier", outlier_state_dict(1, 24))]
+    if only:
+        jobs = [j for j in jobs if j[1] == only]
+    model = None
+    for name, wname, sd in jobs:
+        if sd is not None:
+            _, M2, model = ref_harness.build_reference_model(sd, num_layers=24)
+            cur_sd = sd
+        evl = pix[name]
+        with torch.no_grad():
+            m32 = model.float()
+            feats = [m32.get_model().feature_adaptor(m32.visval_encode(e.float()[None]))[0] for e in evl]
+            tokens = M2.get_spatio_temporal_features(feats)
+            lhs = m32.get_model().visual_tower.visual_tower(evl[0].float()[None]).last_hidden_state[0]
+            mb = model.to(torch.bfloat16)
+            fb = [mb.get_model().feature_adaptor(mb.visval_encode(e[None]))[0] for e in evl]
+            tb = M2.get_spatio_temporal_features(fb).float()
+            model.float()
+        d = (tb - tokens).abs().max().item()
+        cos = torch.nn.functional.cosine_similarity(tb.flatten(), tokens.flatten(), dim=0).item()
+        wsum = float(sum(v.double().abs().sum() for v in cur_sd.values()))
+        px = torch.stack(evl).view(torch.int16).numpy().view(np.uint16)
+        out = os.path.join(OUT, f"tokens_full_{name}_{wname}.npz")
+        np.savez_compressed(out, tokens_f16=tokens.numpy().astype(np.float16), pix_sha=hashlib.sha256(px.tobytes()).hexdigest(),
+                            lhs_absmax_per_channel=lhs.abs().amax(0).numpy(), absmax=np.float32(tokens.abs().max()),
+                            std=np.float32(tokens.std()), weight_abs_sum=np.float64(wsum),
+                            bf16_max_abs=np.float32(d), bf16_cosine=np.float32(cos),
+                            tokens_rows=tokens[[0, 4, 5, 300, 581]].numpy())
+        print(name, wname, "tokens absmax", float(tokens.abs().max()), "std", float(tokens.std()),
+              "| last_hidden_state channel absmax: median", float(lhs.abs().amax(0).median()), "max", float(lhs.abs().amax(0).max()),
+              "| torch-bf16 vs fp32 max-abs", d, "cos", cos, "|", os.path.getsize(out) >> 10, "KiB")
+
+
 def make_splice_golden():
     """Multimodal splice (model/EventChatModel.py:355-465) through the REAL reference: a small-vocab
     EventChatModel with a seeded bf16-representable embedding table and an identity feature_adaptor
@@ -372,6 +446,10 @@ def make_negwins_golden():
     np.savez_compressed(os.path.join(OUT, "negwins.npz"), **out)
     print("negwins.npz:", len(out), "frames")
 
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "tokens_full":
+    make_full_token_goldens(sys.argv[2] if len(sys.argv) > 2 else None)
+    sys.exit(0)
 
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "negwins":

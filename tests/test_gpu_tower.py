@@ -219,6 +219,58 @@ def test_fused_events_to_tokens(frontends, dev):
         fe.visual_tokens(x[:3], y[:3], p[:3], torch.tensor([0, 3], dtype=torch.int64, device=dev), (480, 640))
 
 
+@pytest.mark.parametrize("case,weights", [("sample1", "random"), ("dsec_000069", "random"), ("dense1m", "random"),
+                                          ("sample1", "outlier")])
+def test_full_token_goldens_24_layers(case, weights, frontends, dev):
+    """events -> tokens, 24 layers, against the FULL [582, 4096] output of the reference model itself
+    (tests/golden/tokens_full_*.npz, float16-packed by oracle/make_golden.py tokens_full): the reference's own sample, a DSEC
+    window, a window of the benchmark workload (dense 1M events), and sample1 under weights with massive-activation channels
+    (~70x the median channel in the last hidden state) and sharply peaked attention heads.  Bound: max-abs 2e-2 and cosine
+    >= 0.999 (north_star); with the outlier weights the reference's OWN bf16 run is at 6.9e-2, so the bound there is that
+    yardstick.  float16 packing of the golden adds at most half an ulp of the largest token (stated per case)."""
+    import hashlib
+    from eventgpt_b200 import events as E
+    from eventgpt_b200.model import EventGPTVisualFrontEnd
+    from eventgpt_b200.weights import outlier_state_dict
+    z = np.load(os.path.join(GOLDEN, f"tokens_full_{case}_{weights}.npz"))
+    if case == "dense1m":
+        from oracle.make_golden import synth_window          # the benchmark's generator, restated next to the golden
+        x, y, p = synth_window(0)
+        ev = dict(x=x, y=y, p=p)
+    else:
+        ev = load_golden_events(case)[0]
+    n = len(ev["x"])
+    xd, yd, pd = (E.to_device(np.ascontiguousarray(ev[k]), dev) for k in "xyp")
+    off = torch.tensor([0, n], dtype=torch.int64, device=dev)
+    # the pixel values that reach the tower are the reference's, bit for bit
+    fr, hw, _, st = E.raster(xd, yd, pd, off, 1, 5, 480, 640)
+    px, _, st = E.preprocess(fr, hw, 480, status=st)
+    E.check_status(st, case)
+    assert hashlib.sha256(px.view(torch.int16).cpu().numpy().view(np.uint16).tobytes()).hexdigest() == str(z["pix_sha"])
+    if weights == "random":
+        sd, fe = frontends(24)
+        own = None
+    else:
+        sd = outlier_state_dict(1, 24)
+        fe = own = EventGPTVisualFrontEnd(sd, dev, num_layers=24)
+    try:
+        assert abs(float(sum(v.double().abs().sum() for v in sd.values())) - float(z["weight_abs_sum"])) < 1e-6 * float(z["weight_abs_sum"])
+        tok = fe.visual_tokens(xd, yd, pd, off, (480, 640))[0].float().cpu()
+    finally:
+        if own is not None:
+            own.close()
+    ref = torch.from_numpy(z["tokens_f16"].astype(np.float32))
+    quant = float(z["absmax"]) * 2.0 ** -11
+    err = (tok - ref).abs().max().item()
+    err_rows = (tok[[0, 4, 5, 300, 581]] - torch.from_numpy(z["tokens_rows"])).abs().max().item()     # fp32 rows of the golden
+    cos = _cos(tok, ref)
+    bound = MAX_ABS if weights == "random" else max(MAX_ABS, float(z["bf16_max_abs"]))
+    print(f"{case}/{weights}: ours-bf16 vs ref-fp32 max-abs {err:.4g} (fp32 rows {err_rows:.4g}, f16 packing <= {quant:.2g}) "
+          f"cos {cos:.6f}; torch-bf16 vs ref-fp32 max-abs {float(z['bf16_max_abs']):.4g} cos {float(z['bf16_cosine']):.6f}")
+    assert tuple(tok.shape) == (582, 4096)
+    assert err < bound + quant and err_rows < bound and cos > MIN_COS
+
+
 def test_full_batch_properties(frontends, dev):
     """BASELINE config 2 shape through the fused call at reduced depth: every window of the batch
     equals the same window processed alone (windows are independent; no cross-window state)."""
