@@ -71,6 +71,7 @@ SIGNATURES = {
     "egpt_pool_workspace_bytes": (_sz, [_i, _i, _i]),
     "egpt_spatio_temporal_pool": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _sz, _vp]),
     "egpt_encode_pool": (_i, [_vp, _vp, _i, _i, _vp, _vp, _sz, _vp]),
+    "egpt_project_pool": (_i, [_vp, _vp, _i, _i, _vp, _vp, _sz, _vp]),
     "egpt_splice_embeddings": (_i, [_vp, _vp, _vp, _i64, _i, _vp, _vp]),
     "egpt_visual_tokens_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "egpt_visual_tokens": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),

@@ -150,10 +150,15 @@ static int run_projector(egpt_handle* hd, int F, TowerWs& w, uint16_t* dst, cuda
 // The projector is Linear -> GELU -> Linear and the pooling is a mean, so the second Linear (affine) commutes with it:
 //   pool(W2 g + b2) = W2 pool(g) + b2.  Pooling the GELU output first shrinks the second projector GEMM from
 // n*577 to n+577 rows per window (5x fewer at n = 5); the adaptor then runs on the same pooled rows.
-static int run_projector_pool_adaptor(egpt_handle* hd, int B, int n, TowerWs& w, uint16_t* out_tokens, cudaStream_t st) {
+// hidden == nullptr: the last hidden state is the fp32 residual stream in ws.h (cast to bf16 first); otherwise bf16 [M,1024]
+static int run_projector_pool_adaptor(egpt_handle* hd, int B, int n, TowerWs& w, uint16_t* out_tokens, cudaStream_t st,
+                                      const uint16_t* hidden = nullptr) {
   const long long M = (long long)B * n * kTok, Mo = (long long)B * (n + kTok);
-  EGPT_TRY(f32_to_bf16(w.h, w.y, M * kHid, st));
-  EGPT_TRY(gemm_bf16(w.y, hd->proj0_w, hd->proj0_b, w.mlp, M, kLlm, kHid, EPI_GELU_BF16, st));
+  if (hidden == nullptr) {
+    EGPT_TRY(f32_to_bf16(w.h, w.y, M * kHid, st));
+    hidden = w.y;
+  }
+  EGPT_TRY(gemm_bf16(hidden, hd->proj0_w, hd->proj0_b, w.mlp, M, kLlm, kHid, EPI_GELU_BF16, st));
   EGPT_TRY(egpt_spatio_temporal_pool(w.mlp, 0, B, n, kTok, kLlm, n, w.pooled, w.pool_partial, w.pool_partial_bytes, st));
   EGPT_TRY(gemm_bf16(w.pooled, hd->proj2_w, hd->proj2_b, w.z, Mo, kLlm, kLlm, EPI_BIAS_BF16, st));
   EGPT_TRY(gemm_bf16(w.z, hd->adaptor_w, hd->adaptor_b, out_tokens, Mo, kLlm, kLlm, EPI_BIAS_BF16, st));
@@ -335,6 +340,19 @@ extern "C" int egpt_encode_pool(egpt_handle* h, const uint16_t* pixel_values, in
   EGPT_TRY(im2col(pixel_values, w.qkv, F, st));
   EGPT_TRY(run_tower_from_patches(h, F, w, st));
   EGPT_TRY(run_projector_pool_adaptor(h, n_windows, n_frames, w, out_tokens, st));
+  return EGPT_OK;
+}
+
+extern "C" int egpt_project_pool(egpt_handle* h, const uint16_t* tower_out, int n_windows, int n_frames,
+                                 uint16_t* out_tokens, void* workspace, size_t workspace_bytes, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  EGPT_CHECK_ARG(h && tower_out && out_tokens && workspace && n_windows > 0 && n_frames > 0 && n_frames <= 8,
+                 "egpt_project_pool: bad arguments (n_frames must be 1..8)");
+  EGPT_CHECK_ARG(((uintptr_t)tower_out & 15) == 0 && ((uintptr_t)out_tokens & 15) == 0, "egpt_project_pool: pointers must be 16-byte aligned");
+  EGPT_TRY(check_device(h, "egpt_project_pool"));
+  const int F = n_windows * n_frames;
+  EGPT_WS_OR_FAIL(F);
+  EGPT_TRY(run_projector_pool_adaptor(h, n_windows, n_frames, w, out_tokens, st, tower_out));
   return EGPT_OK;
 }
 

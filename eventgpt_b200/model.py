@@ -299,6 +299,19 @@ class EventGPTVisualFrontEnd:
                                      E.stream_ptr(x.device)), "egpt_encode_pool")
         return out
 
+    def project_pool(self, tower_out, n_frames=E.N_FRAMES):
+        """Cached tower outputs [B*n, 577, 1024] (``tower``'s result) -> event_features [B, n+577, 4096]: projector, adaptor
+        and pooling of the list branch (model/EventChatModel.py:199, 335-342) without re-running the tower."""
+        x = self._bf16(tower_out)
+        if x.ndim != 3 or tuple(x.shape[1:]) != (TOKENS, HID) or x.shape[0] % n_frames:
+            raise ValueError(f"expected [B*{n_frames},577,1024], got {tuple(x.shape)}")
+        B = x.shape[0] // n_frames
+        out = torch.empty((B, n_frames + TOKENS, LLM), dtype=torch.bfloat16, device=x.device)
+        ws = self._ws(x.shape[0])
+        check(lib().egpt_project_pool(self._handle, E.ptr(x), B, n_frames, E.ptr(out), E.ptr(ws), ws.numel(),
+                                      E.stream_ptr(x.device)), "egpt_project_pool")
+        return out
+
     def prepare_inputs_labels_for_multimodal(self, embed_table, input_ids, position_ids, attention_mask, past_key_values,
                                              labels, event_tensors=None, event_image_sizes=None, event_features=None):
         """model/EventChatModel.py:309-465 with the LLM's embedding table passed in (this front end does not own

@@ -18,6 +18,8 @@
  *   - calls are asynchronous on `stream` (a cudaStream_t passed as void*), never
  *     synchronise, install no host callbacks, and keep no global mutable state:
  *     concurrent calls on different streams with different workspaces are safe.
+ *     The one exception to "scratch comes from the caller" and to "no shared state"
+ *     is egpt_raster_static (its comment below says what it shares and when calls race).
  *   - conditions the reference turns into Python exceptions (an empty slice ->
  *     ValueError from y.max(), common/common.py:65) are data dependent; they are
  *     written to a caller-provided device `status` word that the host checks
@@ -94,6 +96,9 @@ int egpt_split_time(const void* x, const void* y, const void* t, const void* p,
 /* packed, row pitch 3*w_f bytes, at out_frames + f*frame_stride; out_hw[f] = {h_f, w_f}.       */
 /* out_counts (optional, may be NULL): int32 [F, 2, H, W] per-pixel event counts (p==0, p!=0),  */
 /* an auxiliary product with no counterpart in the reference.                                   */
+/* Preconditions (checked): out_frames and workspace 16-byte aligned; H, W < 65535; a band of   */
+/* 16 rows of the sensor (16*W bytes) must fit in shared memory (W <= 12800); at most 65535     */
+/* frames per call.  A slice may hold any number of events (no per-slice index is kept).        */
 size_t egpt_raster_frame_stride(int H, int W);   /* bytes between frames: 3*H*W rounded up to 256 */
 size_t egpt_raster_workspace_bytes(int n_windows, int n_frames, int H, int W);
 int egpt_raster(const void* x, const void* y, const void* p, int x_dtype, int y_dtype, int p_dtype,
@@ -106,7 +111,7 @@ int egpt_raster(const void* x, const void* y, const void* p, int x_dtype, int y_
 /* that are not allowed to create device memory: a sensor-acquisition or plug-in thread that    */
 /* was handed its input and output buffers by the host application and must not call cudaMalloc */
 /* (it would stall the device the application is sharing, and it can fail at a moment the       */
-/* thread has no way to recover from).  The key planes that egpt_raster keeps in a caller       */
+/* thread has no way to recover from).  The scratch planes that egpt_raster keeps in a caller    */
 /* workspace live here in a fixed array inside the library, so the call allocates nothing and   */
 /* takes no workspace argument.  Limits and rules:                                              */
 /*   - n_windows * n_frames * H * W <= egpt_raster_static_max_keys() (= 5*720*1280: one 5-frame */
@@ -116,7 +121,7 @@ int egpt_raster(const void* x, const void* y, const void* p, int x_dtype, int y_
 /*     current); make that first call before starting any stream capture.                       */
 /*   - all calls on a device share the one array: two calls that may overlap on the GPU         */
 /*     (different streams, different threads) race -- serialise them.  The array keeps the last */
-/*     call's keys; each call clears the part it uses before rasterising.                       */
+/*     call's planes; a call writes every plane it later reads in full, so nothing is inherited.*/
 /*   - per-pixel counts are not offered here; everything else is as in egpt_raster.             */
 int64_t egpt_raster_static_max_keys(void);
 int egpt_raster_static(const void* x, const void* y, const void* p, int x_dtype, int y_dtype, int p_dtype,
@@ -201,6 +206,14 @@ int egpt_spatio_temporal_pool(const void* features, int is_f32, int batch, int t
 /* same up to rounding).                                                           */
 int egpt_encode_pool(egpt_handle* h, const uint16_t* pixel_values, int n_windows, int n_frames,
                      uint16_t* out_tokens, void* workspace, size_t workspace_bytes, void* stream);
+
+/* a-6 (second half) .. a-8 on cached tower outputs              model/EventChatModel.py:199, 335-342 */
+/* tower_out bf16 [B*n,577,1024] (what egpt_tower returned) -> tokens bf16 [B, n+577, 4096]:       */
+/* visual_projector, feature_adaptor and the pooling without running the tower again; same op      */
+/* order as egpt_encode_pool (pooled before the second projector linear).  n_frames <= 8, like     */
+/* egpt_encode_pool and egpt_visual_tokens (the reference's callers use 5; :119 of common.py).     */
+int egpt_project_pool(egpt_handle* h, const uint16_t* tower_out, int n_windows, int n_frames,
+                      uint16_t* out_tokens, void* workspace, size_t workspace_bytes, void* stream);
 
 /* f-1  multimodal splice of prepare_inputs_labels_for_multimodal  model/EventChatModel.py:355-465 */
 /* One gather builds inputs_embeds [rows = B*L_out, c] (bf16): row i copies embed_table[src[i]]    */
