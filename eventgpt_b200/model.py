@@ -220,6 +220,11 @@ class EventGPTVisualFrontEnd:
         check(lib().egpt_create(C.byref(w), dev.index or 0, C.byref(self._handle)), "egpt_create")
         del keep
 
+    @property
+    def handle_value(self):
+        """The egpt_handle* as a Python int: what the ``torch.ops.eventgpt_b200.*`` operators take as ``handle``."""
+        return int(self._handle.value)
+
     def close(self):
         if getattr(self, "_handle", None) and self._handle.value:
             lib().egpt_destroy(self._handle)

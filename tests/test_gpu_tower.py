@@ -531,3 +531,41 @@ def test_two_threads_two_streams(frontends, dev):
     assert not errs, errs
     for k in range(2):
         assert torch.equal(out[k], alone[k]), k
+
+
+def test_torch_custom_ops(frontends, dev):
+    """torch.ops.eventgpt_b200.* (eventgpt_b200/ops.py): the operators the patched reference calls
+    (inference.py:49-63 -> process_event_data; model/EventChatModel.py:326-345 -> encode_events) return what the Python
+    mirror returns, and pass torch.library.opcheck (schema, fake tensor, dispatch registration)."""
+    import eventgpt_b200.ops  # noqa: F401
+    from eventgpt_b200 import events as E
+    ops = torch.ops.eventgpt_b200
+    sd, fe = frontends(2)
+    ev = load_golden_events("synthetic_000003")[0]
+    n = len(ev["t"])
+    x, y, p = (E.to_device(ev[k], dev) for k in "xyp")
+    off = torch.tensor([0, n // 2, n], dtype=torch.int64, device=dev)
+    H, W = int(ev["y"].max()) + 1, int(ev["x"].max()) + 1
+    tok, hw, st = ops.visual_tokens(fe.handle_value, x, y, p, off, 5, H, W)
+    assert int(st.item()) == 0
+    assert torch.equal(tok, fe.visual_tokens(x, y, p, off, (H, W)))
+    fr, hw2, st = ops.raster(x, y, p, off, 5, H, W, 0, False)
+    assert torch.equal(hw, hw2)
+    pix, st = ops.preprocess(fr, hw2, H)
+    assert torch.equal(ops.encode_pool(fe.handle_value, pix, 5), tok)
+    assert torch.equal(ops.project_pool(fe.handle_value, fe.tower(pix), 5), tok)
+    feats = ops.feature_adaptor(fe.handle_value, ops.visval_encode(fe.handle_value, pix))
+    pooled = ops.spatio_temporal_pool(feats.reshape(2, 5, 577, 4096), 5)
+    assert (pooled.float() - tok.float()).abs().max().item() < 2 * MAX_ABS          # reference op order vs fused order
+    table = torch.randn(50, 4096, device=dev).bfloat16()
+    src = torch.tensor([3, -2, -3, -1, 7], dtype=torch.int32, device=dev)
+    out = ops.splice(table, tok, src)
+    assert torch.equal(out[0], table[3]) and torch.equal(out[1], tok[0, 0]) and torch.equal(out[2], tok[0, 1])
+    assert not out[3].any() and torch.equal(out[4], table[7])
+    tests = ("test_schema", "test_faketensor", "test_autograd_registration")
+    torch.library.opcheck(ops.visual_tokens.default, (fe.handle_value, x, y, p, off, 5, H, W), test_utils=tests)
+    torch.library.opcheck(ops.raster.default, (x, y, p, off, 5, H, W, 0, False), test_utils=tests)
+    torch.library.opcheck(ops.encode_pool.default, (fe.handle_value, pix, 5), test_utils=tests)
+    torch.library.opcheck(ops.splice.default, (table, tok, src), test_utils=tests)
+    # cached tower outputs through the Python mirror too
+    assert torch.equal(fe.project_pool(fe.tower(pix)), tok)
