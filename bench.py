@@ -6,10 +6,12 @@ events (x, y, p) -> 5 RGB frames -> CLIP preprocessing -> ViT-L/14-336 tower -> 
 adaptor -> spatio-temporal pooling -> tokens [B, 582, 4096] (+ the final token gather for N > 1).
 Workload = BASELINE.json configs[1]: 50 ms windows, 1M events at 640x480, batch 32 per GPU, bf16.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config 1|2|3|4]
 
 N > 1 is launched by torchrun (one rank per GPU); rank 0 prints ONE JSON line.
-`--impl reference` times the CPU port of the reference (oracle/) on the host cores.
+`--impl reference` times the CPU port of the reference (oracle/) on the host cores, one window of the
+configured size per step.  `--config` picks another BASELINE.json config (2: 2M-event windows, 256 in
+total; 3: raster-only sweep at 1280x720; 4: tokens + multimodal splice, 64 in total); default 1.
 """
 import argparse
 import json
@@ -25,12 +27,24 @@ sys.path.insert(0, ROOT)
 
 METRIC = "event_windows_per_s_to_visual_tokens"
 UNIT = "windows/s"
-H, W = 480, 640
-EVENTS_PER_WINDOW = 1_000_000
-BATCH_PER_GPU = int(os.environ.get("EGPT_BENCH_BATCH", "32"))     # windows per GPU and step (BASELINE configs[1]: 32); the override is a tuning aid
 N_FRAMES = 5
 GFLOP_PER_WINDOW = 2127.4            # tower 1909.6 + projector 121.0 + adaptor 96.8 (reference op order)
-WORKLOAD = f"synthetic 50 ms windows, 1M events at 640x480, batch {BATCH_PER_GPU} per GPU, bf16 (BASELINE configs[1])"
+CHUNK = int(os.environ.get("EGPT_BENCH_BATCH", "32"))     # windows per library call (BASELINE configs[1]: 32); the override is a tuning aid
+
+# BASELINE.json configs by index.  1 is the driver's default (the metric is quoted on it); 2 and 4 fix the TOTAL batch and
+# shard it over the GPUs (strong scaling); 3 is the raster-only sweep (its own metric, see run_sweep).
+CONFIGS = {
+    1: dict(events=1_000_000, H=480, W=640, per_gpu=CHUNK, total=None, scaling="weak", splice=False,
+            workload=f"synthetic 50 ms windows, 1M events at 640x480, batch {CHUNK} per GPU, bf16 (BASELINE configs[1])"),
+    2: dict(events=2_000_000, H=480, W=640, per_gpu=None, total=256, scaling="strong", splice=False,
+            workload="DSEC-shaped 640x480, 2M events/window, batch 256 in total sharded over the GPUs, bf16 (BASELINE configs[2])"),
+    4: dict(events=1_000_000, H=480, W=640, per_gpu=None, total=64, scaling="strong", splice=True,
+            workload="full visual-token stage feeding EventGPT-7B prefill: events -> tokens -> spliced inputs_embeds [B,641,4096], "
+                     "random-init weights, batch 64 in total sharded over the GPUs, bf16 (BASELINE configs[4])"),
+}
+H, W = 480, 640
+EVENTS_PER_WINDOW = 1_000_000
+WORKLOAD = CONFIGS[1]["workload"]
 
 
 def synth_window(global_index, n_events=EVENTS_PER_WINDOW, h=H, w=W):
@@ -117,34 +131,76 @@ def cpu_port_window(sd, ev, threads):
     return {"raster_s": t1 - t0, "preprocess_s": t2 - t1, "tower_s": t3 - t2, "total_s": t3 - t0}
 
 
+def _raster_one_window(job):
+    """Worker of the process-per-core raster baseline: the reference's loop on one window."""
+    index, n_events, h, w = job
+    from oracle import events as oev
+    x, y, p = synth_window(index, n_events, h, w)
+    t0 = time.perf_counter()
+    oev.get_event_images_list({"x": x, "y": y, "p": p, "t": np.zeros(n_events, np.int8)}, N_FRAMES,
+                              raster=oev.generate_event_image_loop)
+    return time.perf_counter() - t0
+
+
+def cpu_raster_all_cores(cfg, cores):
+    """One process per core, each rasterising an independent window of the configured size with the reference's loop
+    (SURVEY.md 8(d)).  Plain child processes of this script (`--raster-worker`), bounded by a timeout; the time is taken
+    inside each worker, so interpreter start-up is not part of it."""
+    job = f"{cfg['events']},{cfg['H']},{cfg['W']}"
+    procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--raster-worker", f"{1000 + i},{job}"],
+                              stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True,
+                              env={**os.environ, "CUDA_VISIBLE_DEVICES": "", "OMP_NUM_THREADS": "1"}) for i in range(cores)]
+    per = []
+    deadline = time.time() + 600
+    for pr in procs:
+        try:
+            out, _ = pr.communicate(timeout=max(1.0, deadline - time.time()))
+            per.append(float(out.strip().splitlines()[-1]))
+        except Exception:
+            pr.kill()
+    if len(per) != cores:
+        return None
+    return {"processes": cores, "windows": cores, "slowest_process_s": float(max(per)),
+            "mevents_per_s": cores * cfg["events"] / float(max(per)) / 1e6,
+            "single_process_mevents_per_s": cfg["events"] / float(np.mean(per)) / 1e6}
+
+
+def cpu_baseline_line(cfg, r, threads, windows, raster_mp=None):
+    per_window = r["total_s"]
+    d = {"value": 1.0 / per_window, "unit": UNIT, "cores": threads, "kind": "port",
+         "sample": f"{windows} window(s) of the configured size ({cfg['events']} events at {cfg['W']}x{cfg['H']}, nothing scaled): "
+                   f"reference loop raster {r['raster_s']:.2f} s (one core, its native form), preprocessing {r['preprocess_s']:.2f} s, "
+                   f"24-layer fp32 tower+projector+adaptor+pooling {r['tower_s']:.2f} s on {threads} threads",
+         "seconds": {k: r[k] for k in ("raster_s", "preprocess_s", "tower_s")}}
+    if raster_mp:
+        d["raster_all_cores"] = raster_mp
+    return d
+
+
 def run_reference(args, rank):
-    """--impl reference: the reference's own CPU algorithm (numpy + torch fp32 port; the Python
-    reference itself cannot travel to the GPU box) on all host threads, one window per step."""
+    """--impl reference: the reference's own CPU algorithm (numpy + torch fp32 port of the Python reference, which cannot
+    travel to the GPU box) on all host threads; one window of the CONFIGURED size per step, nothing extrapolated."""
     if rank != 0:
         return
-    import torch
     from eventgpt_b200.weights import random_state_dict
+    cfg = CONFIGS[args.config]
     threads = os.cpu_count() or 1
     sd = random_state_dict(0, 24)
-    # bounded sample: 200k-event windows (the raster loop is linear in events: 2.2 s per 1M),
-    # reported per window of the configured size by scaling the raster term only
-    sample_events = 200_000
     times = []
     for i in range(args.warmup + args.steps):
-        x, y, p = synth_window(i, sample_events)
-        r = cpu_port_window(sd, {"x": x, "y": y, "p": p, "t": np.arange(sample_events)}, threads)
+        x, y, p = synth_window(i, cfg["events"], cfg["H"], cfg["W"])
+        r = cpu_port_window(sd, {"x": x, "y": y, "p": p, "t": np.zeros(cfg["events"], np.int8)}, threads)
         if i >= args.warmup:
             times.append(r)
-    scale = EVENTS_PER_WINDOW / sample_events
-    per_window = float(np.mean([t["raster_s"] * scale + t["preprocess_s"] + t["tower_s"] for t in times]))
-    value = 1.0 / per_window
-    sample = (f"{args.steps} windows of {sample_events} events at {W}x{H} (raster loop time scaled x{scale:g} to "
-              f"{EVENTS_PER_WINDOW} events; preprocessing and 24-layer fp32 tower unscaled)")
+    mean = {k: float(np.mean([t[k] for t in times])) for k in times[0]}
+    value = 1.0 / mean["total_s"]
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": per_window * 1e3, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": mean["total_s"] * 1e3, "higher_is_better": True, "scaling": cfg["scaling"],
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "windows_per_step": 1, "host_threads": threads},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "config": {"workload": cfg["workload"], "events_per_window": cfg["events"], "sensor": [cfg["H"], cfg["W"]],
+                       "frames_per_window": N_FRAMES, "windows_per_step": 1, "host_threads": threads,
+                       "weights": "random-init CLIP ViT-L/14-336 + projector + adaptor"},
+            "cpu_baseline": cpu_baseline_line(cfg, mean, threads, args.steps, cpu_raster_all_cores(cfg, threads)),
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -153,35 +209,52 @@ def run_reference(args, rank):
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
-    from eventgpt_b200 import _lib, events as E, sharding
-    from eventgpt_b200.model import EventGPTVisualFrontEnd
+    from eventgpt_b200 import _lib, sharding
+    from eventgpt_b200.model import EventGPTVisualFrontEnd, splice_event_features
+    from eventgpt_b200.pipeline import VisualTokenStream
     from eventgpt_b200.weights import random_state_dict
 
+    cfg = CONFIGS[args.config]
+    H, W, EV = cfg["H"], cfg["W"], cfg["events"]
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    B = BATCH_PER_GPU
-    B_total = B * world
+    B_total = cfg["total"] if cfg["total"] else cfg["per_gpu"] * world
     lo, hi = sharding.shard_bounds(B_total, world, rank)
+    n_local = hi - lo
+    assert B_total % world == 0, "the token gather wants equal shards"
+    chunks = [(c, min(c + CHUNK, n_local)) for c in range(0, n_local, CHUNK)]      # windows per library call
+    cmax = max(e - b for b, e in chunks)
 
     # synthetic events of this rank's windows, in pinned host memory
-    n_ev = (hi - lo) * EVENTS_PER_WINDOW
+    n_ev = n_local * EV
     hx = torch.empty(n_ev, dtype=torch.uint16).pin_memory()
     hy = torch.empty(n_ev, dtype=torch.uint16).pin_memory()
     hp = torch.empty(n_ev, dtype=torch.uint8).pin_memory()
     for j, wi in enumerate(range(lo, hi)):
-        x, y, p = synth_window(wi)
-        s = slice(j * EVENTS_PER_WINDOW, (j + 1) * EVENTS_PER_WINDOW)
-        hx[s], hy[s], hp[s] = torch.from_numpy(x), torch.from_numpy(y), torch.from_numpy(p)
-    hoff = (torch.arange(0, hi - lo + 1, dtype=torch.int64) * EVENTS_PER_WINDOW).pin_memory()
+        x, y, p = synth_window(wi, EV, H, W)
+        sl = slice(j * EV, (j + 1) * EV)
+        hx[sl], hy[sl], hp[sl] = torch.from_numpy(x), torch.from_numpy(y), torch.from_numpy(p)
+    hoffs = [(torch.arange(0, e - b + 1, dtype=torch.int64) * EV).pin_memory() for b, e in chunks]
 
     fe = EventGPTVisualFrontEnd(random_state_dict(0, 24), dev, num_layers=24)
-    dx, dy, dp, doff = (t.to(dev) for t in (hx, hy, hp, hoff))
+    dx, dy, dp = (t.to(dev) for t in (hx, hy, hp))
+    doffs = [h.to(dev) for h in hoffs]
     # two token / gather buffer pairs: with more than one GPU the final all_gather of step i runs on NCCL's stream while step
     # i+1 computes (the hot path itself has no collective; the gather only delivers the result)
-    tokens = [torch.empty((hi - lo, N_FRAMES + 577, 4096), dtype=torch.bfloat16, device=dev) for _ in range(2)]
-    gathered = [torch.empty((B_total, N_FRAMES + 577, 4096), dtype=torch.bfloat16, device=dev) for _ in range(2)] if world > 1 else None
+    T = N_FRAMES + 577
+    tokens = [torch.empty((n_local, T, 4096), dtype=torch.bfloat16, device=dev) for _ in range(2)]
+    gathered = [torch.empty((B_total, T, 4096), dtype=torch.bfloat16, device=dev) for _ in range(2)] if world > 1 else None
+    splice_in = None
+    if cfg["splice"]:
+        # EventGPT-7B prefill input (model/EventChatModel.py:355-465): 59 text tokens + the <event> slot -> 641 rows
+        g = torch.Generator(device="cpu").manual_seed(4)
+        table = (torch.randn(32000, 4096, generator=g) * 0.02).bfloat16().to(dev)
+        ids = torch.randint(3, 32000, (cmax, 60), generator=g)
+        ids[:, 35] = -200
+        splice_in = (table, ids.to(dev))
+        embeds = [None, None]
     pending = [None, None]
     state = {"i": 0}
 
@@ -191,7 +264,11 @@ def run_ours(args, rank, world, local_rank):
         if pending[k] is not None:
             pending[k].wait()                         # the gather that last read tokens[k] has finished
             pending[k] = None
-        fe.visual_tokens(dx, dy, dp, doff, (H, W), out=tokens[k], check_flags=False)
+        for (b, e), doff in zip(chunks, doffs):
+            fe.visual_tokens(dx[b * EV:e * EV], dy[b * EV:e * EV], dp[b * EV:e * EV], doff, (H, W), out=tokens[k][b:e],
+                             check_flags=False)
+            if splice_in is not None:
+                embeds[k] = splice_event_features(splice_in[0], splice_in[1][:e - b], None, None, None, tokens[k][b:e])[2]
         if world > 1:
             pending[k] = dist.all_gather_into_tensor(gathered[k], tokens[k], async_op=True)
 
@@ -201,14 +278,21 @@ def run_ours(args, rank, world, local_rank):
                 pending[k].wait()
                 pending[k] = None
 
-    from eventgpt_b200.pipeline import VisualTokenStream
-    stream = VisualTokenStream(fe, n_ev, hi - lo, (H, W))
-    gather = (lambda tok, slot: dist.all_gather_into_tensor(gathered[slot], tok, async_op=True)) if world > 1 else None
+    stream = VisualTokenStream(fe, cmax * EV, cmax, (H, W))
+    gathered_e2e = [torch.empty((cmax * world, T, 4096), dtype=torch.bfloat16, device=dev) for _ in range(2)] if world > 1 else None
+
+    def post(tok, slot):
+        if splice_in is not None:
+            embeds[slot] = splice_event_features(splice_in[0], splice_in[1][:tok.shape[0]], None, None, None, tok)[2]
+        if world > 1:
+            return dist.all_gather_into_tensor(gathered_e2e[slot][:tok.shape[0] * world], tok, async_op=True)
+        return None
 
     def step_e2e():
         # public host-fed API: pinned host events in, tokens out to pinned host memory, every step; the H2D of
         # the next batch and the D2H of the previous one overlap this batch's compute (three streams, two slots)
-        stream.submit(hx, hy, hp, hoff, post=gather)
+        for (b, e), hoff in zip(chunks, hoffs):
+            stream.submit(hx[b * EV:e * EV], hy[b * EV:e * EV], hp[b * EV:e * EV], hoff, post=post)
 
     def barrier():
         if world > 1:
@@ -236,7 +320,8 @@ def run_ours(args, rank, world, local_rank):
     for _ in range(args.warmup):
         step_resident()
     finish_gathers()
-    fe.visual_tokens(dx, dy, dp, doff, (H, W), out=tokens[0], check_flags=True)     # raises on any device-side flag
+    b0, e0 = chunks[0]
+    fe.visual_tokens(dx[:e0 * EV], dy[:e0 * EV], dp[:e0 * EV], doffs[0], (H, W), out=tokens[0][:e0], check_flags=True)   # raises on any device-side flag
     _lib.launch_count(True)
     total_ms = timed(step_resident, args.steps, tail=finish_gathers)       # the last gathers complete inside the timed region
     clocks = sampler.stop() if rank == 0 else None
@@ -247,7 +332,7 @@ def run_ours(args, rank, world, local_rank):
     stream.drain()
     # the last batch's D2H is inside the timed region: the compute stream waits for the copy-out stream
     e2e_ms = timed(step_e2e, args.steps, tail=stream.join)
-    stream.drain()
+    stream.drain()                           # also raises if any timed batch set a device-side flag
 
     # per-kernel-family device time, CUDA events on the launching stream (second pass, K steps)
     _lib.profile_enable(True)
@@ -263,63 +348,104 @@ def run_ours(args, rank, world, local_rank):
         ms_step = total_ms / args.steps
         value = B_total / (ms_step * 1e-3)
         gemm_ms, gemm_n, gemm_flop = prof["gemm"]
-        attn_ms, attn_n, attn_flop = prof["attention"]
         rast_ms, rast_n, _ = prof["raster"]
         peak_tf = pk.get("bf16_tflops_sustained", pk.get("bf16_tflops"))
         achieved_tf = gemm_flop / (gemm_ms * 1e-3) / 1e12 if gemm_ms else 0.0
-        raster_bytes = (hi - lo) * (5 * EVENTS_PER_WINDOW + 15 * H * W) * args.steps
+        raster_bytes = n_local * (5 * EV + 15 * H * W) * args.steps
         raster_gbs = raster_bytes / (rast_ms * 1e-3) / 1e9 if rast_ms else 0.0
-        traffic = None
-        try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "gemm_traffic.json")))["dram_bytes_per_launch"]
-        except Exception:
-            pass
-        prof_total = sum(v[0] for v in prof.values())
+
+        def from_profiles(name, key):
+            try:
+                return json.load(open(os.path.join(ROOT, "profiles", name)))[key]
+            except Exception:
+                return None
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": cfg["scaling"], "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD, "windows_per_gpu": B, "windows_total": B_total, "events_per_window": EVENTS_PER_WINDOW,
+            "config": {"workload": cfg["workload"], "windows_per_gpu": n_local, "windows_total": B_total, "events_per_window": EV,
+                       "windows_per_library_call": cmax,
                        "sensor": [H, W], "frames_per_window": N_FRAMES, "weights": "random-init CLIP ViT-L/14-336 + projector + adaptor",
                        "parallelism": f"dp{world} (windows sharded, final all_gather of tokens overlapped with the next step)" if world > 1 else "dp1",
-                       "l2": "per-step working set (~4 GB of activations, 160 MB of events) exceeds the 126 MB L2"},
+                       "l2": "per-step working set (~4 GB of activations, >= 160 MB of events) exceeds the 126 MB L2"},
             "tflops_algorithmic": value * GFLOP_PER_WINDOW / 1e3,
             "e2e": {"value": B_total / (e2e_ms / args.steps * 1e-3), "unit": UNIT,
-                    "h2d_bytes_per_step": int(hx.numel() * 2 + hy.numel() * 2 + hp.numel() + hoff.numel() * 8),
-                    "d2h_bytes_per_step": int(tokens[0].numel() * 2),
-                    "api": "eventgpt_b200.pipeline.VisualTokenStream.submit (H2D / compute / D2H on three streams, two slots)"},
+                    "h2d_bytes_per_step": int(hx.numel() * 2 + hy.numel() * 2 + hp.numel() + sum(h.numel() for h in hoffs) * 8),
+                    "d2h_bytes_per_step": int(tokens[0].numel() * 2 + 4 * len(chunks)),
+                    "api": "eventgpt_b200.pipeline.VisualTokenStream.submit (H2D / compute / D2H on three streams, two slots; "
+                           "tokens and the status word come back to pinned host memory"
+                           + ("; the spliced inputs_embeds stay on the device, where the LLM prefill reads them)" if cfg["splice"] else ")")},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"kernel": "gemm2_bf16_kernel (tcgen05 cta_group::2, all tower/projector/adaptor linears)", "bound": "tensor",
                          "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-                         "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": traffic,
+                         "frac": achieved_tf / peak_tf if peak_tf else None,
+                         "traffic": from_profiles("gemm_traffic.json", "dram_bytes_per_launch"),
+                         "traffic_source": "profiles/gemm_traffic.json: dram__bytes_read+write per launch from an ncu --set full capture "
+                                           "(not measured by this run)",
                          "peak_source": f"{pk_src} bf16_tflops_sustained (kernel timed inside a long step)",
                          "launches": gemm_n, "avg_launch_ms": gemm_ms / gemm_n if gemm_n else None,
-                         "share_of_step": gemm_ms / prof_total if prof_total else None},
-            "raster_roofline": {"kernel": "raster_scatter + raster_colourise (+ key-plane memset)", "bound": "hbm",
+                         "share_of_step": (gemm_ms / args.steps) / ms_step if ms_step else None},
+            "raster_roofline": {"kernel": "raster_tile_kernel + raster_colourise_kernel (one egpt_raster call)", "bound": "hbm",
                                 "achieved": raster_gbs, "peak": pk.get("hbm_gbs"), "unit": "GB/s",
                                 "frac": raster_gbs / pk["hbm_gbs"] if pk.get("hbm_gbs") else None,
-                                "mevents_per_s": (hi - lo) * EVENTS_PER_WINDOW * args.steps / (rast_ms * 1e-3) / 1e6 if rast_ms else None,
-                                "bytes_per_window": 5 * EVENTS_PER_WINDOW + 15 * H * W, "traffic": None},
+                                "mevents_per_s": n_local * EV * args.steps / (rast_ms * 1e-3) / 1e6 if rast_ms else None,
+                                "bytes_per_window": 5 * EV + 15 * H * W,
+                                "traffic": from_profiles("raster_traffic.json", "dram_bytes_per_call"),
+                                "traffic_source": "profiles/raster_traffic.json: dram__bytes_read+write of both kernels from an ncu "
+                                                  "--set full --cache-control none capture of the same 32 x 1M-event call"},
             "kernel_ms_per_step": {k: v[0] / args.steps for k, v in prof.items() if v[1]},
         }
         if world == 1 and not args.no_cpu_baseline:
-            # bounded CPU sample on the host cores: one window, reduced event count for the Python raster loop
+            # bounded CPU sample on the host cores: ONE window of the configured size, nothing scaled
             threads = os.cpu_count() or 1
-            sample_events = 200_000
-            x, y, p = synth_window(0, sample_events)
-            r = cpu_port_window(random_state_dict(0, 24), {"x": x, "y": y, "p": p, "t": np.arange(sample_events)}, threads)
-            scale = EVENTS_PER_WINDOW / sample_events
-            per_window = r["raster_s"] * scale + r["preprocess_s"] + r["tower_s"]
-            line["cpu_baseline"] = {"value": 1.0 / per_window, "unit": UNIT, "cores": threads, "kind": "port",
-                                    "sample": f"1 window: raster loop on {sample_events} events scaled x{scale:g} "
-                                              f"({r['raster_s']*scale:.2f} s), preprocessing {r['preprocess_s']:.2f} s, "
-                                              f"24-layer fp32 tower+projector+adaptor+pooling {r['tower_s']:.2f} s"}
+            x, y, p = synth_window(0, EV, H, W)
+            r = cpu_port_window(random_state_dict(0, 24), {"x": x, "y": y, "p": p, "t": np.zeros(EV, np.int8)}, threads)
+            line["cpu_baseline"] = cpu_baseline_line(cfg, r, threads, 1, cpu_raster_all_cores(cfg, threads))
         print(json.dumps(line), flush=True)
     fe.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def run_sweep(args, rank, world, local_rank):
+    """--config 3: BASELINE configs[3], rasterisation only, 10^4 .. 10^8 events per window at 1280x720, one 5-frame window per
+    call, events resident on the device; every GPU runs the same sweep (replicas).  metric = raster Mevents/s at 10^8."""
+    import torch
+    from eventgpt_b200 import _lib, events as E
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    Hs, Ws = 720, 1280
+    pk, pk_src = peaks()
+    rows = []
+    for exp in range(4, 9):
+        n = 10 ** exp
+        x, y, p = synth_window(exp, n, Hs, Ws)
+        xd, yd, pd = (torch.from_numpy(a).to(dev) for a in (x, y, p))
+        off = torch.tensor([0, n], dtype=torch.int64, device=dev)
+        for _ in range(max(3, args.warmup)):
+            fr, hw, _, st = E.raster(xd, yd, pd, off, 1, N_FRAMES, Hs, Ws)
+        E.check_status(st, "sweep")
+        reps = args.steps if exp < 8 else max(2, args.steps // 2)
+        _lib.profile_enable(True)
+        for _ in range(reps):
+            E.raster(xd, yd, pd, off, 1, N_FRAMES, Hs, Ws)
+        ms = _lib.profile_collect()["raster"][0] / reps
+        _lib.profile_enable(False)
+        by = 5 * n + 15 * Hs * Ws
+        rows.append({"events": n, "us": ms * 1e3, "mevents_per_s": n / ms / 1e3, "gbs": by / ms / 1e6,
+                     "frac": by / ms / 1e6 / pk["hbm_gbs"]})
+    if rank == 0:
+        top = rows[-1]
+        print(json.dumps({"metric": "raster_mevents_per_s", "value": top["mevents_per_s"] * world, "unit": "Mevents/s", "n_gpus": world,
+                          "steps": args.steps, "warmup": args.warmup, "ms_per_step": top["us"] / 1e3, "higher_is_better": True,
+                          "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                          "config": {"workload": "rasterisation-only sweep 10^4-10^8 events/window at 1280x720, one 5-frame window per "
+                                                 "call (BASELINE configs[3]); value = the 10^8 point; replicas on every GPU",
+                                     "l2": "inputs of the 10^7 and 10^8 points exceed L2; below that the call is launch/frame-write bound"},
+                          "roofline": {"bound": "hbm", "achieved": top["gbs"], "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": top["frac"],
+                                       "traffic": None, "peak_source": pk_src}, "sweep": rows}), flush=True)
 
 
 def main():
@@ -328,13 +454,21 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", type=int, default=1, choices=[1, 2, 3, 4],
+                    help="index into BASELINE.json configs (1 = the driver's default; 3 = raster-only sweep)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--raster-worker", default=None, help=argparse.SUPPRESS)
     args = ap.parse_args()
+    if args.raster_worker:
+        print(_raster_one_window(tuple(int(v) for v in args.raster_worker.split(","))), flush=True)
+        return
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
+        if args.config == 3:
+            args.config = 1
         run_reference(args, rank)
         return
     if world != args.gpus:
@@ -343,7 +477,10 @@ def main():
             cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                    "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__)] + sys.argv[1:]
             sys.exit(subprocess.call(cmd))
-    run_ours(args, rank, world, local_rank)
+    if args.config == 3:
+        run_sweep(args, rank, world, local_rank)
+    else:
+        run_ours(args, rank, world, local_rank)
 
 
 if __name__ == "__main__":
