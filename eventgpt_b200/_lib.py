@@ -58,6 +58,9 @@ SIGNATURES = {
     "egpt_raster_frame_stride": (_sz, [_i, _i]),
     "egpt_raster_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "egpt_raster": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "egpt_raster_ranges": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "egpt_clip_bounds": (_i, [_vp, _i, _i64, _i64, _i64, _i64, _i, _vp, _vp]),
+    "egpt_ms_window_bounds": (_i, [_vp, _i, _i64, _i64, _i64, _i64, _i, _vp, _vp, _vp]),
     "egpt_raster_static_max_keys": (_i64, []),
     "egpt_raster_static": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "egpt_preprocess_workspace_bytes": (_sz, [_i, _i]),
@@ -75,6 +78,7 @@ SIGNATURES = {
     "egpt_splice_embeddings": (_i, [_vp, _vp, _vp, _i64, _i, _vp, _vp]),
     "egpt_visual_tokens_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "egpt_visual_tokens": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "egpt_visual_tokens_ranges": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "egpt_gemm_bf16": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "egpt_attention": (_i, [_vp, _i, _vp, _vp]),
 }

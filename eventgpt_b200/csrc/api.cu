@@ -365,12 +365,17 @@ extern "C" size_t egpt_visual_tokens_workspace_bytes(int n_windows, int n_frames
          align_up(egpt_preprocess_workspace_bytes(F, H), 1024) + tower_ws_bytes(F) + 8 * 1024;
 }
 
-extern "C" int egpt_visual_tokens(egpt_handle* h, const void* x, const void* y, const void* p, int x_dtype, int y_dtype,
-                                  int p_dtype, const int64_t* window_offsets, int n_windows, int n_frames, int H, int W,
-                                  uint16_t* out_tokens, int32_t* out_hw, int32_t* status, void* workspace,
-                                  size_t workspace_bytes, void* stream) {
-  cudaStream_t st = (cudaStream_t)stream;
-  EGPT_CHECK_ARG(h && x && y && p && window_offsets && out_tokens && out_hw && status && workspace,
+namespace egpt {
+int raster_impl(const void* x, const void* y, const void* p, int x_dtype, int y_dtype, int p_dtype, const int64_t* window_offsets,
+                int off_stride, int n_windows, int n_frames, int mode, int H, int W, int fixed_canvas, uint8_t* out_frames,
+                int32_t* out_hw, int32_t* out_counts, int32_t* status, void* workspace, size_t workspace_bytes, bool shrink_to_fit,
+                cudaStream_t stream);
+
+static int visual_tokens_impl(egpt_handle* h, const void* x, const void* y, const void* p, int x_dtype, int y_dtype, int p_dtype,
+                              const int64_t* windows, int off_stride, int n_windows, int n_frames, int H, int W,
+                              uint16_t* out_tokens, int32_t* out_hw, int32_t* status, void* workspace, size_t workspace_bytes,
+                              cudaStream_t st) {
+  EGPT_CHECK_ARG(h && x && y && p && windows && out_tokens && out_hw && status && workspace,
                  "egpt_visual_tokens: null pointer argument");
   EGPT_CHECK_ARG(n_windows > 0 && n_frames > 0 && n_frames <= 8 && H > 0 && W > 0, "egpt_visual_tokens: bad shape");
   EGPT_TRY(check_device(h, "egpt_visual_tokens"));
@@ -392,11 +397,28 @@ extern "C" int egpt_visual_tokens(egpt_handle* h, const void* x, const void* y, 
   if (!a.ok()) { set_error("egpt_visual_tokens: workspace carve failed"); return EGPT_ERR_WORKSPACE; }
   TowerWs w;
   if (!carve_tower_ws(tower_ws, tws, F, &w)) { set_error("egpt_visual_tokens: tower workspace carve failed"); return EGPT_ERR_WORKSPACE; }
-  EGPT_TRY(egpt_raster(x, y, p, x_dtype, y_dtype, p_dtype, window_offsets, n_windows, n_frames, EGPT_RASTER_LAST_WINS, H, W,
-                       0, frames, out_hw, nullptr, status, raster_ws, rws, st));
+  EGPT_TRY(raster_impl(x, y, p, x_dtype, y_dtype, p_dtype, windows, off_stride, n_windows, n_frames, EGPT_RASTER_LAST_WINS, H, W,
+                       0, frames, out_hw, nullptr, status, raster_ws, rws, false, st));
   // resized + normalised pixels go straight into the im2col layout of the patch GEMM
   EGPT_TRY(egpt_preprocess(frames, frame_stride, out_hw, F, H, nullptr, w.qkv, status, pre_ws, pws, st));
   EGPT_TRY(run_tower_from_patches(h, F, w, st));
   EGPT_TRY(run_projector_pool_adaptor(h, n_windows, n_frames, w, out_tokens, st));
   return EGPT_OK;
+}
+}  // namespace egpt
+
+extern "C" int egpt_visual_tokens(egpt_handle* h, const void* x, const void* y, const void* p, int x_dtype, int y_dtype,
+                                  int p_dtype, const int64_t* window_offsets, int n_windows, int n_frames, int H, int W,
+                                  uint16_t* out_tokens, int32_t* out_hw, int32_t* status, void* workspace,
+                                  size_t workspace_bytes, void* stream) {
+  return visual_tokens_impl(h, x, y, p, x_dtype, y_dtype, p_dtype, window_offsets, 1, n_windows, n_frames, H, W, out_tokens, out_hw,
+                            status, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int egpt_visual_tokens_ranges(egpt_handle* h, const void* x, const void* y, const void* p, int x_dtype, int y_dtype,
+                                         int p_dtype, const int64_t* window_bounds, int n_windows, int n_frames, int H, int W,
+                                         uint16_t* out_tokens, int32_t* out_hw, int32_t* status, void* workspace,
+                                         size_t workspace_bytes, void* stream) {
+  return visual_tokens_impl(h, x, y, p, x_dtype, y_dtype, p_dtype, window_bounds, 2, n_windows, n_frames, H, W, out_tokens, out_hw,
+                            status, workspace, workspace_bytes, (cudaStream_t)stream);
 }

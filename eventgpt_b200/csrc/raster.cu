@@ -44,8 +44,11 @@ struct SliceInfo {
 };
 
 // slice i of a window [s, e): k = (e-s)/n, [s+i*k, s+(i+1)*k), last slice takes the remainder
-__device__ __forceinline__ SliceInfo slice_bounds(const int64_t* __restrict__ offsets, int window, int i, int n) {
-  long long s = offsets[window], e = offsets[window + 1];
+// (window w = events [offsets[w*stride], offsets[w*stride + 1]): stride 1 = CSR offsets, stride 2 = (start, end) pairs,
+// which may overlap)
+__device__ __forceinline__ SliceInfo slice_bounds(const int64_t* __restrict__ offsets, int stride, int window, int i, int n) {
+  long long s = offsets[(size_t)window * stride], e = offsets[(size_t)window * stride + 1];
+  if (e < s) e = s;
   long long k = (e - s) / n;
   SliceInfo r;
   r.start = s + (long long)i * k;
@@ -113,6 +116,7 @@ struct RasterArgs {
   const void *x, *y, *p;
   int xdt, ydt, pdt;
   const int64_t* offsets;
+  int off_stride;
   int n_frames, H, W, fixed_canvas;
   TilePlan plan;
   uint32_t* scratch;        // [frame][K][plane_words]
@@ -224,7 +228,7 @@ raster_tile_kernel(const __grid_constant__ RasterArgs a) {
     frame = a.plan.head_frames + item / ((long long)R * K);
   }
   const int window = (int)(frame / a.n_frames), fi = (int)(frame % a.n_frames);
-  const SliceInfo sl = slice_bounds(a.offsets, window, fi, a.n_frames);
+  const SliceInfo sl = slice_bounds(a.offsets, a.off_stride, window, fi, a.n_frames);
   if (sl.end <= sl.start) {
     if (band == 0 && range == 0 && tid == 0) atomicOr(a.status, EGPT_FLAG_EMPTY_SLICE);
     return;
@@ -454,7 +458,8 @@ __device__ __forceinline__ void bulk_store_1d(void* gdst, const void* ssrc, unsi
 
 __global__ void __launch_bounds__(kColThreads)
 raster_colourise_kernel(const uint32_t* __restrict__ scratch, const int32_t* __restrict__ out_hw,
-                        const int64_t* __restrict__ offsets, int n_frames, const __grid_constant__ TilePlan plan, int W,
+                        const int64_t* __restrict__ offsets, int off_stride, int n_frames,
+                        const __grid_constant__ TilePlan plan, int W,
                         uint8_t* __restrict__ out_frames, size_t frame_stride) {
   __shared__ __align__(128) uint8_t stage[2][kColChunk];
   const long long frame = blockIdx.y;
@@ -462,7 +467,7 @@ raster_colourise_kernel(const uint32_t* __restrict__ scratch, const int32_t* __r
   const int h = out_hw[2 * frame], w = out_hw[2 * frame + 1];
   const long long npix = (long long)h * w;
   if (npix == 0) return;
-  const SliceInfo sl = slice_bounds(offsets, (int)(frame / n_frames), (int)(frame % n_frames), n_frames);
+  const SliceInfo sl = slice_bounds(offsets, off_stride, (int)(frame / n_frames), (int)(frame % n_frames), n_frames);
   const int K = frame < plan.head_frames ? 1 : plan.K;
   const int n_ranges = sl.end > sl.start ? ranges_of(((sl.end + 7) >> 3) - (sl.start >> 3), K) : 0;
   const unsigned plane_words = plan.plane_words;
@@ -702,8 +707,8 @@ static int launch_tiles(const RasterArgs& a, long long items, cudaStream_t strea
 }
 
 // shrink_to_fit: use fewer event ranges per slice when the scratch is smaller than the query asks for
-static int raster_impl(const void* x, const void* y, const void* p, int x_dtype, int y_dtype, int p_dtype,
-                       const int64_t* window_offsets, int n_windows, int n_frames, int mode, int H, int W,
+int raster_impl(const void* x, const void* y, const void* p, int x_dtype, int y_dtype, int p_dtype,
+                       const int64_t* window_offsets, int off_stride, int n_windows, int n_frames, int mode, int H, int W,
                        int fixed_canvas, uint8_t* out_frames, int32_t* out_hw, int32_t* out_counts, int32_t* status,
                        void* workspace, size_t workspace_bytes, bool shrink_to_fit, cudaStream_t stream) {
   EGPT_CHECK_ARG(x && y && p && window_offsets && out_frames && out_hw && status && workspace,
@@ -736,7 +741,7 @@ static int raster_impl(const void* x, const void* y, const void* p, int x_dtype,
   // egpt_profile_collect supplies them, so only time is recorded here
   ProfScope prof(PROF_RASTER, 0.0, stream);
   a.x = x; a.y = y; a.p = p; a.xdt = x_dtype; a.ydt = y_dtype; a.pdt = p_dtype;
-  a.offsets = window_offsets; a.n_frames = n_frames; a.H = H; a.W = W; a.fixed_canvas = fixed_canvas;
+  a.offsets = window_offsets; a.off_stride = off_stride; a.n_frames = n_frames; a.H = H; a.W = W; a.fixed_canvas = fixed_canvas;
   a.scratch = (uint32_t*)workspace; a.out_hw = out_hw; a.out_counts = out_counts; a.status = status;
   const bool fast = x_dtype == EGPT_U16 && y_dtype == EGPT_U16 && p_dtype == EGPT_U8 &&
                     ((uintptr_t)x % 16 == 0) && ((uintptr_t)y % 16 == 0) && ((uintptr_t)p % 8 == 0);
@@ -760,8 +765,8 @@ static int raster_impl(const void* x, const void* y, const void* p, int x_dtype,
   const int want = (int)((kNumSMs * 6 + F - 1) / F);
   if (cgrid > want) cgrid = want;
   if (cgrid < 1) cgrid = 1;
-  raster_colourise_kernel<<<dim3(cgrid, (unsigned)F), kColThreads, 0, stream>>>(a.scratch, out_hw, window_offsets, n_frames,
-                                                                                a.plan, W, out_frames, frame_stride);
+  raster_colourise_kernel<<<dim3(cgrid, (unsigned)F), kColThreads, 0, stream>>>(a.scratch, out_hw, window_offsets, off_stride,
+                                                                                n_frames, a.plan, W, out_frames, frame_stride);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
 }
@@ -771,8 +776,70 @@ extern "C" int egpt_raster(const void* x, const void* y, const void* p, int x_dt
                            const int64_t* window_offsets, int n_windows, int n_frames, int mode, int H, int W,
                            int fixed_canvas, uint8_t* out_frames, int32_t* out_hw, int32_t* out_counts,
                            int32_t* status, void* workspace, size_t workspace_bytes, void* stream) {
-  return raster_impl(x, y, p, x_dtype, y_dtype, p_dtype, window_offsets, n_windows, n_frames, mode, H, W, fixed_canvas,
+  return raster_impl(x, y, p, x_dtype, y_dtype, p_dtype, window_offsets, 1, n_windows, n_frames, mode, H, W, fixed_canvas,
                      out_frames, out_hw, out_counts, status, workspace, workspace_bytes, false, (cudaStream_t)stream);
+}
+
+extern "C" int egpt_raster_ranges(const void* x, const void* y, const void* p, int x_dtype, int y_dtype, int p_dtype,
+                                  const int64_t* window_bounds, int n_windows, int n_frames, int mode, int H, int W,
+                                  int fixed_canvas, uint8_t* out_frames, int32_t* out_hw, int32_t* out_counts,
+                                  int32_t* status, void* workspace, size_t workspace_bytes, void* stream) {
+  return raster_impl(x, y, p, x_dtype, y_dtype, p_dtype, window_bounds, 2, n_windows, n_frames, mode, H, W, fixed_canvas,
+                     out_frames, out_hw, out_counts, status, workspace, workspace_bytes, false, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------
+// Window / clip bounds of a long time-sorted recording, on the device.
+// ------------------------------------------------------------------------------------------
+namespace egpt {
+// first index i in [0, n) with t[i] >= v (n if none)
+__device__ __forceinline__ long long lower_bound_t(const void* __restrict__ t, int tdt, long long n, long long v) {
+  long long lo = 0, hi = n;
+  while (lo < hi) {
+    const long long mid = (lo + hi) >> 1;
+    if (load_int(t, tdt, mid) < v) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+__global__ void clip_bounds_kernel(const void* __restrict__ t, int tdt, long long n, long long first_us, long long interval_us,
+                                   long long step_us, int n_clips, int64_t* __restrict__ out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_clips) return;
+  const long long s = first_us + (long long)c * step_us;
+  out[2 * c] = lower_bound_t(t, tdt, n, s);
+  out[2 * c + 1] = lower_bound_t(t, tdt, n, s + interval_us);
+}
+
+__global__ void ms_bounds_kernel(const void* __restrict__ ms_to_idx, int dt, long long n_ms, long long first_ms, long long window_ms,
+                                 long long step_ms, int n_windows, int64_t* __restrict__ out, int32_t* __restrict__ status) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_windows) return;
+  const long long a = first_ms + (long long)c * step_ms, b = a + window_ms;
+  if (a < 0 || b >= n_ms) { atomicOr(status, EGPT_FLAG_OUT_OF_RANGE); out[2 * c] = out[2 * c + 1] = 0; return; }
+  out[2 * c] = load_int(ms_to_idx, dt, a);
+  out[2 * c + 1] = load_int(ms_to_idx, dt, b);
+}
+}  // namespace egpt
+
+extern "C" int egpt_clip_bounds(const void* t, int t_dtype, int64_t n_events, int64_t first_us, int64_t interval_us,
+                                int64_t step_us, int n_clips, int64_t* out_bounds, void* stream) {
+  EGPT_CHECK_ARG(t && out_bounds && dtype_size(t_dtype), "egpt_clip_bounds: bad pointer or dtype");
+  EGPT_CHECK_ARG(n_events >= 0 && interval_us > 0 && step_us > 0 && n_clips > 0, "egpt_clip_bounds: bad sizes");
+  clip_bounds_kernel<<<(n_clips + 127) / 128, 128, 0, (cudaStream_t)stream>>>(t, t_dtype, n_events, first_us, interval_us,
+                                                                             step_us, n_clips, out_bounds);
+  EGPT_LAUNCH_CHECK();
+  return EGPT_OK;
+}
+
+extern "C" int egpt_ms_window_bounds(const void* ms_to_idx, int dtype, int64_t n_ms, int64_t first_ms, int64_t window_ms,
+                                     int64_t step_ms, int n_windows, int64_t* out_bounds, int32_t* status, void* stream) {
+  EGPT_CHECK_ARG(ms_to_idx && out_bounds && status && dtype_size(dtype), "egpt_ms_window_bounds: bad pointer or dtype");
+  EGPT_CHECK_ARG(n_ms > 0 && window_ms >= 0 && step_ms > 0 && n_windows > 0, "egpt_ms_window_bounds: bad sizes");
+  ms_bounds_kernel<<<(n_windows + 127) / 128, 128, 0, (cudaStream_t)stream>>>(ms_to_idx, dtype, n_ms, first_ms, window_ms, step_ms,
+                                                                             n_windows, out_bounds, status);
+  EGPT_LAUNCH_CHECK();
+  return EGPT_OK;
 }
 
 extern "C" size_t egpt_split_time_workspace_bytes(int64_t n_events, int max_windows) {
@@ -882,7 +949,7 @@ extern "C" int egpt_raster_static(const void* x, const void* y, const void* p, i
   EGPT_TRY(static_scratch_address(&scratch));
   // every partial plane that is read is written in full by its band CTAs first, so whatever the
   // previous call left in the array is harmless; the number of event ranges shrinks to what fits
-  return raster_impl(x, y, p, x_dtype, y_dtype, p_dtype, window_offsets, n_windows, n_frames, mode, H, W, fixed_canvas,
+  return raster_impl(x, y, p, x_dtype, y_dtype, p_dtype, window_offsets, 1, n_windows, n_frames, mode, H, W, fixed_canvas,
                      out_frames, out_hw, nullptr, status, scratch,
                      (size_t)(kStaticMaxKeys + kStaticSlackWords) * sizeof(uint32_t), true, (cudaStream_t)stream);
 }

@@ -85,9 +85,31 @@ def check_status(status, what):
         raise ValueError(f"{what}: frame too large for the resize filter (32 taps)")
 
 
+def clip_bounds(t, first_us, interval_us, step_us, n_clips):
+    """egpt_clip_bounds: (start, end) event indices int64 [n_clips, 2] of the clips [first + c*step, first + c*step + interval)
+    of a time-sorted device tensor ``t`` (build_my_egpt_dsec_seq.py:137-202 with step = interval // 2)."""
+    out = torch.empty((n_clips, 2), dtype=torch.int64, device=t.device)
+    check(lib().egpt_clip_bounds(ptr(t), _CODE_OF_TORCH[t.dtype], t.numel(), int(first_us), int(interval_us), int(step_us),
+                                 n_clips, ptr(out), stream_ptr(t.device)), "egpt_clip_bounds")
+    return out
+
+
+def ms_window_bounds(ms_to_idx, first_ms, window_ms, step_ms, n_windows, status=None):
+    """egpt_ms_window_bounds: (start, end) int64 [n_windows, 2] from DSEC's ``ms_to_idx`` device tensor (dataset/io.py:68-87)."""
+    dev = ms_to_idx.device
+    out = torch.empty((n_windows, 2), dtype=torch.int64, device=dev)
+    if status is None:
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+    check(lib().egpt_ms_window_bounds(ptr(ms_to_idx), _CODE_OF_TORCH[ms_to_idx.dtype], ms_to_idx.numel(), int(first_ms),
+                                      int(window_ms), int(step_ms), n_windows, ptr(out), ptr(status), stream_ptr(dev)),
+          "egpt_ms_window_bounds")
+    return out, status
+
+
 def raster(x, y, p, window_offsets, n_windows, n_frames, H, W, mode=_lib.RASTER_LAST_WINS, fixed_canvas=False,
-           counts=False, status=None):
-    """egpt_raster on device tensors.  Returns (frames uint8 [F, stride], hw int32 [F,2], counts|None, status)."""
+           counts=False, status=None, ranges=False):
+    """egpt_raster on device tensors.  Returns (frames uint8 [F, stride], hw int32 [F,2], counts|None, status).
+    ``ranges=True``: ``window_offsets`` is int64 [n_windows, 2] of (start, end) pairs (egpt_raster_ranges)."""
     dev = x.device
     F = n_windows * n_frames
     stride = lib().egpt_raster_frame_stride(H, W)
@@ -98,10 +120,11 @@ def raster(x, y, p, window_offsets, n_windows, n_frames, H, W, mode=_lib.RASTER_
         status = torch.zeros(1, dtype=torch.int32, device=dev)
     nws = lib().egpt_raster_workspace_bytes(n_windows, n_frames, H, W)
     ws = Workspace.get(dev, "raster", nws)
-    check(lib().egpt_raster(ptr(x), ptr(y), ptr(p), _CODE_OF_TORCH[x.dtype], _CODE_OF_TORCH[y.dtype],
-                            _CODE_OF_TORCH[p.dtype], ptr(window_offsets), n_windows, n_frames, mode, H, W,
-                            1 if fixed_canvas else 0, ptr(frames), ptr(hw), ptr(cnt), ptr(status), ptr(ws), ws.numel(),
-                            stream_ptr(dev)), "egpt_raster")
+    fn = lib().egpt_raster_ranges if ranges else lib().egpt_raster
+    check(fn(ptr(x), ptr(y), ptr(p), _CODE_OF_TORCH[x.dtype], _CODE_OF_TORCH[y.dtype],
+             _CODE_OF_TORCH[p.dtype], ptr(window_offsets), n_windows, n_frames, mode, H, W,
+             1 if fixed_canvas else 0, ptr(frames), ptr(hw), ptr(cnt), ptr(status), ptr(ws), ws.numel(),
+             stream_ptr(dev)), "egpt_raster")
     return frames, hw, cnt, status
 
 

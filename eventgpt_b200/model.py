@@ -354,15 +354,17 @@ class EventGPTVisualFrontEnd:
 
     # ---- fused path: events -> tokens ------------------------------------------------------------
     def visual_tokens(self, x, y, p, window_offsets, sensor_size, n_frames=E.N_FRAMES, out=None, check_flags=True,
-                      status=None):
+                      status=None, ranges=False):
         """process_event_data (common/common.py:110-129) + the list branch (:326-343) for a batch of
         windows, device resident end to end.  x, y, p: device integer tensors holding all windows back
         to back; window_offsets: int64 [B+1] on the device.  Returns tokens bf16 [B, n_frames+577, 4096].
         ``status`` (int32 [1] on the device, zeroed by the caller) receives the data-dependent flags when the caller
-        checks them later itself (``check_flags=False``: no host synchronisation here)."""
+        checks them later itself (``check_flags=False``: no host synchronisation here).
+        ``ranges=True``: ``window_offsets`` holds (start, end) pairs, int64 [B, 2], of possibly overlapping windows of one
+        recording (``events.clip_bounds`` / ``events.ms_window_bounds``) -- egpt_visual_tokens_ranges."""
         dev = x.device
         H, W = int(sensor_size[0]), int(sensor_size[1])
-        B = window_offsets.numel() - 1
+        B = window_offsets.shape[0] if ranges else window_offsets.numel() - 1
         if out is None:
             out = torch.empty((B, n_frames + TOKENS, LLM), dtype=torch.bfloat16, device=dev)
         hw = torch.empty((B * n_frames, 2), dtype=torch.int32, device=dev)
@@ -370,10 +372,11 @@ class EventGPTVisualFrontEnd:
             status = torch.zeros(1, dtype=torch.int32, device=dev)
         nws = lib().egpt_visual_tokens_workspace_bytes(B, n_frames, H, W)
         ws = E.Workspace.get(dev, "fused", nws)
-        check(lib().egpt_visual_tokens(self._handle, E.ptr(x), E.ptr(y), E.ptr(p), E._CODE_OF_TORCH[x.dtype],
-                                       E._CODE_OF_TORCH[y.dtype], E._CODE_OF_TORCH[p.dtype], E.ptr(window_offsets), B,
-                                       n_frames, H, W, E.ptr(out), E.ptr(hw), E.ptr(status), E.ptr(ws), ws.numel(),
-                                       E.stream_ptr(dev)), "egpt_visual_tokens")
+        fn = lib().egpt_visual_tokens_ranges if ranges else lib().egpt_visual_tokens
+        check(fn(self._handle, E.ptr(x), E.ptr(y), E.ptr(p), E._CODE_OF_TORCH[x.dtype],
+                 E._CODE_OF_TORCH[y.dtype], E._CODE_OF_TORCH[p.dtype], E.ptr(window_offsets), B,
+                 n_frames, H, W, E.ptr(out), E.ptr(hw), E.ptr(status), E.ptr(ws), ws.numel(),
+                 E.stream_ptr(dev)), "egpt_visual_tokens")
         if check_flags:
             E.check_status(status, "visual_tokens")
         return out

@@ -41,8 +41,17 @@ class VisualTokenStream:
         self.ev_d2h = [torch.cuda.Event() for _ in range(depth)]
         self.posted = [None] * depth
         self.count = 0
+        self.dt = None                                     # timestamps, only for submit_recording()
 
-    def submit(self, hx, hy, hp, hoff, post=None):
+    def submit_recording(self, hx, hy, hp, ht, first_us, interval_us, step_us, n_clips, post=None):
+        """Enqueue one time-sorted recording (pinned host tensors; ``ht`` any integer dtype) cut into ``n_clips`` clips
+        [first_us + c*step_us, +interval_us) ON THE DEVICE: the (start, end) pairs come from ``egpt_clip_bounds`` (two binary
+        searches per clip) and ``egpt_visual_tokens_ranges`` rasterises the possibly overlapping clips straight from the one
+        copy of the events -- the 50 %-overlap clips of build_my_egpt_dsec_seq.py:137-202 with step_us = interval_us // 2,
+        consecutive dataset/io.py:68-87 windows with step_us = interval_us.  Same slots, copies and flags as ``submit``."""
+        return self.submit(hx, hy, hp, None, post=post, ht=ht, clips=(int(first_us), int(interval_us), int(step_us), int(n_clips)))
+
+    def submit(self, hx, hy, hp, hoff, post=None, ht=None, clips=None):
         """Enqueue one batch (pinned host tensors: x, y uint16; p uint8; window offsets int64 [B+1]).
         Returns the slot whose pinned ``htok[slot][:B]`` holds the tokens once ``wait(slot)`` returns.
         ``post(tokens, slot)``, if given, runs right after the batch's compute was enqueued (e.g. the final all_gather of a
@@ -50,7 +59,9 @@ class VisualTokenStream:
         buffer is written again and in ``drain``."""
         i, s = self.count, self.count % self.depth
         self.count += 1
-        n, B = hx.numel(), hoff.numel() - 1
+        n, B = hx.numel(), (clips[3] if clips else hoff.numel() - 1)
+        if clips and (self.dt is None or self.dt[0].dtype != ht.dtype):
+            self.dt = [torch.empty(self.dx[0].numel(), dtype=ht.dtype, device=self.dev) for _ in range(self.depth)]
         compute = torch.cuda.current_stream(self.dev)
         if i >= self.depth:
             self.s_in.wait_event(self.ev_done[s])          # slot's device inputs were consumed by batch i-depth
@@ -60,7 +71,10 @@ class VisualTokenStream:
             self.dx[s][:n].copy_(hx, non_blocking=True)
             self.dy[s][:n].copy_(hy, non_blocking=True)
             self.dp[s][:n].copy_(hp, non_blocking=True)
-            self.doff[s][:B + 1].copy_(hoff, non_blocking=True)
+            if clips:
+                self.dt[s][:n].copy_(ht, non_blocking=True)
+            else:
+                self.doff[s][:B + 1].copy_(hoff, non_blocking=True)
             self.ev_h2d[s].record(self.s_in)
         compute.wait_event(self.ev_h2d[s])
         if i >= self.depth:
@@ -71,8 +85,12 @@ class VisualTokenStream:
         if self.unchecked[s]:
             self._check(s)                                 # nobody waited for the slot's previous batch: its flags are due now
         self.status[s].zero_()
-        self.fe.visual_tokens(self.dx[s][:n], self.dy[s][:n], self.dp[s][:n], self.doff[s][:B + 1], self.sensor,
-                              n_frames=self.n_frames, out=self.tok[s][:B], check_flags=False, status=self.status[s])
+        if clips:
+            windows = E.clip_bounds(self.dt[s][:n], clips[0], clips[1], clips[2], B)
+        else:
+            windows = self.doff[s][:B + 1]
+        self.fe.visual_tokens(self.dx[s][:n], self.dy[s][:n], self.dp[s][:n], windows, self.sensor, n_frames=self.n_frames,
+                              out=self.tok[s][:B], check_flags=False, status=self.status[s], ranges=bool(clips))
         if post is not None:
             self.posted[s] = post(self.tok[s][:B], s)      # e.g. the final all_gather of a multi-GPU job
         self.ev_done[s].record(compute)

@@ -107,6 +107,31 @@ int egpt_raster(const void* x, const void* y, const void* p, int x_dtype, int y_
                 uint8_t* out_frames, int32_t* out_hw, int32_t* out_counts,
                 int32_t* status, void* workspace, size_t workspace_bytes, void* stream);
 
+/* f-2  the same rasterisation over (start, end) pairs -- windows that may overlap -- instead of CSR */
+/* offsets: window b = events [window_bounds[2b], window_bounds[2b+1]) of ONE time-ordered recording.   */
+/* This is how the 50 %-overlap clips of build_my_egpt_dsec_seq.py:137-202 and the DSEC windows of      */
+/* dataset/io.py:68-87 are rasterised without copying the shared events (egpt_clip_bounds /             */
+/* egpt_ms_window_bounds below produce the pairs on the device).                                        */
+int egpt_raster_ranges(const void* x, const void* y, const void* p, int x_dtype, int y_dtype, int p_dtype,
+                       const int64_t* window_bounds, int n_windows, int n_frames,
+                       int mode, int H, int W, int fixed_canvas,
+                       uint8_t* out_frames, int32_t* out_hw, int32_t* out_counts,
+                       int32_t* status, void* workspace, size_t workspace_bytes, void* stream);
+
+/* f-2  clip bounds of a time-SORTED recording   feasible/my_egpt_dsec_dataset/build_my_egpt_dsec_seq.py:137-202 */
+/* clip c covers times [first_us + c*step_us, first_us + c*step_us + interval_us): out_bounds[c] = {first event  */
+/* index with t >= start, first index with t >= end} (two binary searches per clip on the device; t any integer  */
+/* dtype).  step_us = interval_us/2 gives the reference's 50 %-overlap clips, step_us = interval_us consecutive   */
+/* windows.  An empty clip has start == end (the reference drops it; egpt_raster flags it as an empty slice).      */
+int egpt_clip_bounds(const void* t, int t_dtype, int64_t n_events, int64_t first_us, int64_t interval_us,
+                     int64_t step_us, int n_clips, int64_t* out_bounds, void* stream);
+
+/* f-2  window bounds from DSEC's per-millisecond index                          dataset/io.py:68-87             */
+/* window c = events [ms_to_idx[first_ms + c*step_ms], ms_to_idx[first_ms + c*step_ms + window_ms]); a window     */
+/* beyond the index sets EGPT_FLAG_OUT_OF_RANGE (the reference's assert on t_max).                                 */
+int egpt_ms_window_bounds(const void* ms_to_idx, int dtype, int64_t n_ms, int64_t first_ms, int64_t window_ms,
+                          int64_t step_ms, int n_windows, int64_t* out_bounds, int32_t* status, void* stream);
+
 /* egpt_raster_static -- no counterpart in the reference.  The same rasterisation for callers   */
 /* that are not allowed to create device memory: a sensor-acquisition or plug-in thread that    */
 /* was handed its input and output buffers by the host application and must not call cudaMalloc */
@@ -231,6 +256,13 @@ int egpt_visual_tokens(egpt_handle* h, const void* x, const void* y, const void*
                        const int64_t* window_offsets, int n_windows, int n_frames, int H, int W,
                        uint16_t* out_tokens, int32_t* out_hw, int32_t* status,
                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* the same from (start, end) pairs of one recording (see egpt_raster_ranges) */
+int egpt_visual_tokens_ranges(egpt_handle* h, const void* x, const void* y, const void* p,
+                              int x_dtype, int y_dtype, int p_dtype,
+                              const int64_t* window_bounds, int n_windows, int n_frames, int H, int W,
+                              uint16_t* out_tokens, int32_t* out_hw, int32_t* status,
+                              void* workspace, size_t workspace_bytes, void* stream);
 
 /* Building block exposed for tests and profiling: C = epilogue(A[M,K] . B[N,K]^T + bias).       */
 /* epilogue: 0 bias -> bf16, 1 bias+QuickGELU -> bf16, 2 bias+GELU(erf) -> bf16,                  */

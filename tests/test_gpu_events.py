@@ -264,6 +264,58 @@ def test_overlap_clips_rasterise_like_reference(dev):
             assert np.array_equal(got[b * 5 + i], want[i]), (b, i)
 
 
+def test_device_clip_bounds_and_ranges_vs_reference_goldens(dev):
+    """Upstream ingestion on the device.  (a) egpt_clip_bounds on the recording of tests/golden/clips.npz gives
+    the clips the reference's own 50 %-overlap splitter produced (build_my_egpt_dsec_seq.py:137-202: first index and event count
+    of every non-empty clip); egpt_raster_ranges rasterises them from the ONE copy of the events, equal to the oracle's frames
+    of each clip.  (b) egpt_ms_window_bounds reproduces the slices the reference's extract_from_h5_by_timewindow cut
+    (tests/golden/dsec_io.npz, dataset/io.py:68-87)."""
+    from eventgpt_b200 import events as E
+    from oracle import events as oev
+    from oracle.make_golden import clips_inputs, io_recording, IO_WINDOWS
+    z = np.load(os.path.join(GOLDEN, "clips.npz"))
+    ev, stamps = clips_inputs()
+    first, interval, step = min(stamps), 50_000, 25_000
+    n_clips = (max(stamps) - interval - first) // step + 1
+    td = E.to_device(ev["t"], dev)
+    bounds = E.clip_bounds(td, first, interval, step, n_clips)
+    b = bounds.cpu().numpy()
+    keep = b[:, 1] > b[:, 0]
+    assert int(keep.sum()) == int(z["a_n"])
+    assert np.array_equal(b[keep, 0], z["a_first"]) and np.array_equal(b[keep, 1] - b[keep, 0], z["a_count"])
+    assert np.array_equal(first + step * np.nonzero(keep)[0], z["a_time_start"])
+    x, y, p = _dev_events(ev, dev)
+    kept = bounds[torch.from_numpy(keep).to(dev)].contiguous()
+    fr, hw, _, st = E.raster(x, y, p, kept, kept.shape[0], 5, 480, 640, ranges=True)
+    E.check_status(st, "clips")
+    got = E.frames_to_numpy(fr, hw)
+    for c, (s_, e_) in enumerate(b[keep]):
+        want = oev.get_event_images_list({k: ev[k][s_:e_] for k in "xypt"}, 5)
+        for i in range(5):
+            assert np.array_equal(got[c * 5 + i], want[i]), (c, i)
+    # an empty clip in the batch is flagged like any empty slice (the reference drops such clips before rasterising)
+    fr, hw, _, st = E.raster(x, y, p, bounds, n_clips, 5, 480, 640, ranges=True)
+    with pytest.raises(ValueError):
+        E.check_status(st, "clips with a hole")
+    # (b) DSEC per-millisecond index
+    zi = np.load(os.path.join(GOLDEN, "dsec_io.npz"))
+    rec = io_recording()
+    off = int(rec["t_offset"])
+    ms = E.to_device(rec["ms_to_idx"], dev)
+    for (t0, t1), want in zip(IO_WINDOWS, zi["windows"]):
+        a_ms, b_ms = (t0 - off) // 1000, (t1 - off) // 1000
+        bd, st = E.ms_window_bounds(ms, a_ms, b_ms - a_ms, 1, 1)
+        assert int(st.item()) == 0
+        s_, e_ = (int(v) for v in bd.cpu().numpy()[0])
+        sl = {k: rec["events"][k][s_:e_] for k in "xypt"}
+        assert e_ - s_ == want[0]
+        if e_ > s_:
+            assert int(sl["t"][0]) + off == want[1] and int(sl["t"][-1]) + off == want[2]
+            assert [int(sl[k].astype(np.int64).sum()) for k in "xyp"] == list(want[3:6])
+    bd, st = E.ms_window_bounds(ms, 0, 50, 50, 9)             # the ninth 50 ms window lies beyond the 400 ms index
+    assert int(st.item()) & 2
+
+
 @pytest.mark.parametrize("h,w", [(1100, 2000), (340, 1900), (1500, 400)])
 def test_preprocess_arbitrary_images_wide_and_deep_filters(h, w, dev):
     """egpt_preprocess on arbitrary uint8 images (the PNG path) at sizes that leave the common fast paths:

@@ -355,6 +355,33 @@ def test_host_fed_stream_matches_direct_call(frontends, dev):
     vs.drain()
 
 
+def test_stream_recording_clips_on_device(frontends, dev):
+    """VisualTokenStream.submit_recording: a time-sorted recording goes to the device once; the 50 %-overlap clip bounds
+    (build_my_egpt_dsec_seq.py:137-202) are found there and the clips' tokens equal those of the host-side clip splitter +
+    ragged batch (eventgpt_b200.io), clip by clip."""
+    from eventgpt_b200 import events as E, io as eio
+    from eventgpt_b200.pipeline import VisualTokenStream
+    sd, fe = frontends(2)
+    rng = np.random.default_rng(33)
+    n, H, W = 90_000, 240, 320
+    t = np.sort(rng.integers(5_000_000, 5_300_000, n)).astype(np.int64)
+    ev = dict(x=rng.integers(0, W, n).astype(np.uint16), y=rng.integers(0, H, n).astype(np.uint16),
+              p=rng.integers(0, 2, n).astype(np.uint8), t=t)
+    stamps = [5_000_000 + 50_000 * i for i in range(7)]
+    clips = eio.split_event_by_time_clips(ev, 50_000, stamps)
+    n_clips = (max(stamps) - 50_000 - min(stamps)) // 25_000 + 1
+    assert len(clips) == n_clips == 11
+    x, y, p, off = eio.clips_to_batch(ev, clips)
+    want = fe.visual_tokens(E.to_device(x, dev), E.to_device(y, dev), E.to_device(p, dev),
+                            torch.tensor(off, dtype=torch.int64, device=dev), (H, W)).cpu()
+    vs = VisualTokenStream(fe, n, n_clips, (H, W))
+    pin = lambda a: torch.from_numpy(a).pin_memory()
+    s = vs.submit_recording(pin(ev["x"]), pin(ev["y"]), pin(ev["p"]), pin(ev["t"]), min(stamps), 50_000, 25_000, n_clips)
+    got = vs.wait(s)[:n_clips].clone()
+    vs.drain()
+    assert torch.equal(got, want)
+
+
 def test_attention_lazy_rescale_and_peaked_rows(dev):
     """The attention kernel keeps a stale row maximum unless a later key block exceeds it by more than 2^8, and then
     rescales its TMEM accumulator in place.  Drive both paths: (a) scores that grow block after block (every block
