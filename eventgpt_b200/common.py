@@ -51,13 +51,21 @@ def get_event_images_list(event_npy, n, sensor_size=None, device=None):
 
 def split_event_by_time(event_npy, time_interval=50000, max_windows=4096, device=None):
     """common/common.py:76-107: list of {'p','t','x','y'} dicts, one per non-empty time bin
-    (t // time_interval), ascending, event order preserved inside a bin."""
+    (t // time_interval), ascending, event order preserved inside a bin.
+    ``max_windows`` bounds the SPAN of bins between the earliest and the latest event (empty bins in between count); a
+    recording with a long gap that exceeds it is split again with the span it really needs, so the result is the
+    reference's either way."""
     dev = E._require_cuda(device)
     p, t, x, y = (np.asarray(event_npy[k]) for k in ("p", "t", "x", "y"))
     if len(t) == 0:
         return []
     xd, yd, td, pd = (E.to_device(a, dev) for a in (x, y, t, p))
     ox, oy, ot, op, offsets, nwin, status = E.split_time(xd, yd, td, pd, time_interval, max_windows)
+    if int(status.item()) & E._lib.FLAG_TOO_MANY_BINS:
+        span = int(t.max()) // int(time_interval) - int(t.min()) // int(time_interval) + 1
+        if span > (1 << 20):
+            raise ValueError(f"split_event_by_time: the stream spans {span} time bins (limit 2^20)")
+        ox, oy, ot, op, offsets, nwin, status = E.split_time(xd, yd, td, pd, time_interval, span)
     E.check_status(status, "split_event_by_time")
     nw = int(nwin.item())
     off = offsets[: nw + 1].cpu().numpy()

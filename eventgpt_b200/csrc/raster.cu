@@ -548,12 +548,20 @@ struct SplitPlan {
   int span_cap;        // capacity of the dense bin table (= max_windows)
 };
 
-__global__ void split_minmax_kernel(const void* __restrict__ t, int tdt, long long n, long long interval,
-                                    long long* __restrict__ minmax) {
+// minimum and maximum TIMESTAMP (the bin is monotone in t, so the division happens once per kernel, not once per event)
+template <bool T64>
+__global__ void split_minmax_kernel(const void* __restrict__ t, int tdt, long long n, long long* __restrict__ minmax) {
   long long lo = 0x7fffffffffffffffLL, hi = -0x7fffffffffffffffLL - 1;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    long long b = floor_div(load_int(t, tdt, i), interval);
-    lo = min(lo, b); hi = max(hi, b);
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += 4 * stride) {
+    long long v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long j = (i + u * stride) < n ? i + u * stride : i;       // past the end: element i again
+      v[u] = T64 ? ((const long long*)t)[j] : load_int(t, tdt, j);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { lo = min(lo, v[u]); hi = max(hi, v[u]); }
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -563,66 +571,133 @@ __global__ void split_minmax_kernel(const void* __restrict__ t, int tdt, long lo
   if ((threadIdx.x & 31) == 0) { atomicMin(minmax, lo); atomicMax(minmax + 1, hi); }
 }
 
+// bin of a timestamp relative to the first bin of the stream.  When the stream spans less than 2^32 us past the start of
+// its first bin (any real recording), the 64-bit floor division becomes one 32-bit division.
+struct BinOf {
+  long long lo, span, t0, interval;
+  unsigned iv32;
+  bool small;
+  __device__ BinOf(const long long* __restrict__ minmax, long long interval_) : interval(interval_) {
+    const long long tmin = minmax[0], tmax = minmax[1];
+    lo = floor_div(tmin, interval);
+    span = floor_div(tmax, interval) - lo + 1;
+    t0 = lo * interval;
+    small = interval < (1LL << 31) && (tmax - t0) < (1LL << 32);
+    iv32 = (unsigned)interval;
+  }
+  __device__ __forceinline__ int operator()(long long tv) const {
+    return small ? (int)((unsigned)(tv - t0) / iv32) : (int)(floor_div(tv, interval) - lo);
+  }
+};
+
 __global__ void split_init_kernel(long long* minmax) {
   minmax[0] = 0x7fffffffffffffffLL;
   minmax[1] = -0x7fffffffffffffffLL - 1;
 }
 
-// one warp per chunk
+// one warp per chunk: zeroes its row of the table (the bin span is known by now), then counts
+template <bool T64>
 __global__ void split_count_kernel(const void* __restrict__ t, int tdt, SplitPlan plan, long long interval,
                                    const long long* __restrict__ minmax, int32_t* __restrict__ table,
                                    int32_t* __restrict__ status) {
   const int chunk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (chunk >= plan.n_chunks) return;
-  const long long lo = minmax[0], span = minmax[1] - lo + 1;
+  const BinOf bin(minmax, interval);
+  const long long span = bin.span;
   if (span > plan.span_cap) { if (lane == 0 && chunk == 0) atomicOr(status, EGPT_FLAG_TOO_MANY_BINS); return; }
   const long long s = (long long)chunk * plan.chunk, e = min(plan.n, s + plan.chunk);
   int32_t* row = table + (size_t)chunk * plan.span_cap;
-  for (long long b0 = s; b0 < e; b0 += 32) {
-    const long long i = b0 + lane;
-    const int rb = i < e ? (int)(floor_div(load_int(t, tdt, i), interval) - lo) : -1;
-    const unsigned m = __match_any_sync(0xffffffffu, rb);
-    if (rb >= 0 && lane == __ffs(m) - 1) row[rb] += __popc(m);
-    __syncwarp();
+  for (long long i = lane; i < span; i += 32) row[i] = 0;
+  __syncwarp();
+  for (long long b0 = s; b0 < e; b0 += 128) {
+    int rb[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {                            // four rows of 32 timestamps in flight
+      const long long i = b0 + u * 32 + lane;
+      rb[u] = i < e ? bin(T64 ? ((const long long*)t)[i] : load_int(t, tdt, i)) : -1;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const unsigned m = __match_any_sync(0xffffffffu, rb[u]);
+      if (rb[u] >= 0 && lane == __ffs(m) - 1) row[rb[u]] += __popc(m);
+      __syncwarp();
+    }
   }
 }
 
-// single CTA: per-bin totals, compaction of non-empty bins into window offsets, then
-// per-(chunk,bin) destination offsets written back into the table.
-__global__ void __launch_bounds__(1024)
-split_scan_kernel(SplitPlan plan, const long long* __restrict__ minmax, int32_t* __restrict__ table,
-                  long long* __restrict__ bin_start, int64_t* __restrict__ out_offsets,
-                  int32_t* __restrict__ out_nwindows, int max_windows) {
-  const long long span = minmax[1] - minmax[0] + 1;
-  if (span > plan.span_cap) { if (threadIdx.x == 0) { *out_nwindows = 0; out_offsets[0] = 0; } return; }
-  for (int rb = threadIdx.x; rb < span; rb += blockDim.x) {
-    long long tot = 0;
-    for (int c = 0; c < plan.n_chunks; ++c) tot += table[(size_t)c * plan.span_cap + rb];
-    bin_start[rb] = tot;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    long long run = 0; int nw = 0;
-    out_offsets[0] = 0;
-    for (int rb = 0; rb < span; ++rb) {
-      const long long c = bin_start[rb];
-      bin_start[rb] = run;
-      run += c;
-      if (c > 0) { ++nw; if (nw <= max_windows) out_offsets[nw] = run; }
-    }
-    *out_nwindows = nw;
-  }
-  __syncthreads();
-  for (int rb = threadIdx.x; rb < span; rb += blockDim.x) {
-    long long run = bin_start[rb];
-    for (int c = 0; c < plan.n_chunks; ++c) {
+// one CTA per time bin: exclusive prefix of the bin's counts over the chunks, in place; the bin's total on the side
+__global__ void __launch_bounds__(256)
+split_column_scan_kernel(SplitPlan plan, long long interval, const long long* __restrict__ minmax, int32_t* __restrict__ table,
+                         long long* __restrict__ bin_total) {
+  const long long span = BinOf(minmax, interval).span;
+  if (span > plan.span_cap) return;
+  __shared__ int warp_sum[8];
+  __shared__ int carry_s;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  for (long long rb = blockIdx.x; rb < span; rb += gridDim.x) {
+    if (tid == 0) carry_s = 0;
+    __syncthreads();
+    for (int c0 = 0; c0 < plan.n_chunks; c0 += 256) {
+      const int c = c0 + tid;
       int32_t* cell = table + (size_t)c * plan.span_cap + rb;
-      const int32_t cnt = *cell;
-      // destinations are < 2^31 per chunk row only when n < 2^31; larger streams are rejected on the host
-      *cell = (int32_t)run;
-      run += cnt;
+      const int v = c < plan.n_chunks ? *cell : 0;
+      int incl = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += u; }
+      if (lane == 31) warp_sum[wid] = incl;
+      __syncthreads();
+      int before = carry_s;
+      for (int w = 0; w < wid; ++w) before += warp_sum[w];
+      if (c < plan.n_chunks) *cell = before + incl - v;
+      __syncthreads();
+      if (tid == 255) carry_s = before + incl;
+      __syncthreads();
     }
+    if (tid == 0) bin_total[rb] = carry_s;
+    __syncthreads();
   }
+}
+
+// single CTA: exclusive prefix of the bin totals (first destination of every bin) and compaction of the non-empty bins
+// into window offsets
+__global__ void __launch_bounds__(1024)
+split_bin_scan_kernel(SplitPlan plan, long long interval, const long long* __restrict__ minmax, long long* __restrict__ bin_start,
+                      int64_t* __restrict__ out_offsets, int32_t* __restrict__ out_nwindows, int max_windows) {
+  const long long span = BinOf(minmax, interval).span;
+  if (span > plan.span_cap) { if (threadIdx.x == 0) { *out_nwindows = 0; out_offsets[0] = 0; } return; }
+  __shared__ long long wsum[32];
+  __shared__ int wcnt[32];
+  __shared__ long long carry_s;
+  __shared__ int carry_n;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) { carry_s = 0; carry_n = 0; out_offsets[0] = 0; }
+  __syncthreads();
+  for (long long r0 = 0; r0 < span; r0 += 1024) {
+    const long long rb = r0 + tid;
+    const long long v = rb < span ? bin_start[rb] : 0;        // holds the bin's total on entry
+    const int ne = v > 0;
+    long long incl = v;
+    int ninc = ne;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const long long u = __shfl_up_sync(0xffffffffu, incl, o);
+      const int un = __shfl_up_sync(0xffffffffu, ninc, o);
+      if (lane >= o) { incl += u; ninc += un; }
+    }
+    if (lane == 31) { wsum[wid] = incl; wcnt[wid] = ninc; }
+    __syncthreads();
+    long long before = carry_s;
+    int nbefore = carry_n;
+    for (int w = 0; w < wid; ++w) { before += wsum[w]; nbefore += wcnt[w]; }
+    if (rb < span) {
+      bin_start[rb] = before + incl - v;
+      if (ne && nbefore + ninc <= max_windows) out_offsets[nbefore + ninc] = before + incl;
+    }
+    __syncthreads();
+    if (tid == 1023) { carry_s = before + incl; carry_n = nbefore + ninc; }
+    __syncthreads();
+  }
+  if (tid == 0) *out_nwindows = carry_n;
 }
 
 __device__ __forceinline__ void copy_elem(void* __restrict__ dst, const void* __restrict__ src, int size,
@@ -635,35 +710,59 @@ __device__ __forceinline__ void copy_elem(void* __restrict__ dst, const void* __
   }
 }
 
+// FAST: t 64-bit, x and y 16-bit, p 8-bit (the layout of the reference's DSEC windows): typed copies
+template <bool FAST>
 __global__ void split_scatter_kernel(const void* __restrict__ x, const void* __restrict__ y,
                                      const void* __restrict__ t, const void* __restrict__ p,
                                      int xs, int ys, int tdt, int ps, SplitPlan plan, long long interval,
                                      const long long* __restrict__ minmax, int32_t* __restrict__ table,
+                                     const long long* __restrict__ bin_start,
                                      void* __restrict__ ox, void* __restrict__ oy, void* __restrict__ ot,
                                      void* __restrict__ op) {
   const int chunk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (chunk >= plan.n_chunks) return;
-  const long long lo = minmax[0], span = minmax[1] - lo + 1;
-  if (span > plan.span_cap) return;
+  const BinOf bin(minmax, interval);
+  if (bin.span > plan.span_cap) return;
   const long long s = (long long)chunk * plan.chunk, e = min(plan.n, s + plan.chunk);
   int32_t* row = table + (size_t)chunk * plan.span_cap;
   const int ts = dtype_size(tdt);
-  for (long long b0 = s; b0 < e; b0 += 32) {
-    const long long i = b0 + lane;
-    const int rb = i < e ? (int)(floor_div(load_int(t, tdt, i), interval) - lo) : -1;
-    const unsigned m = __match_any_sync(0xffffffffu, rb);
-    const int leader = __ffs(m) - 1;
-    int base = 0;
-    if (rb >= 0 && lane == leader) { base = row[rb]; row[rb] = base + __popc(m); }
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (rb >= 0) {
-      const long long d = (long long)base + __popc(m & ((1u << lane) - 1u));
-      copy_elem(ox, x, xs, d, i);
-      copy_elem(oy, y, ys, d, i);
-      copy_elem(ot, t, ts, d, i);
-      copy_elem(op, p, ps, d, i);
+  for (long long b0 = s; b0 < e; b0 += 128) {
+    int rb[4];
+    long long tv[4];
+    uint16_t xv[4], yv[4];
+    uint8_t pv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = b0 + u * 32 + lane;
+      if (FAST) {
+        if (i < e) { tv[u] = ((const long long*)t)[i]; xv[u] = ((const uint16_t*)x)[i]; yv[u] = ((const uint16_t*)y)[i]; pv[u] = ((const uint8_t*)p)[i]; }
+        else tv[u] = 0;
+        rb[u] = i < e ? bin(tv[u]) : -1;
+      } else {
+        rb[u] = i < e ? bin(load_int(t, tdt, i)) : -1;
+      }
     }
-    __syncwarp();
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = b0 + u * 32 + lane;
+      const unsigned m = __match_any_sync(0xffffffffu, rb[u]);
+      const int leader = __ffs(m) - 1;
+      int base = 0;
+      if (rb[u] >= 0 && lane == leader) { base = row[rb[u]]; row[rb[u]] = base + __popc(m); }
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (rb[u] >= 0) {
+        const long long d = bin_start[rb[u]] + base + __popc(m & ((1u << lane) - 1u));
+        if (FAST) {
+          ((long long*)ot)[d] = tv[u]; ((uint16_t*)ox)[d] = xv[u]; ((uint16_t*)oy)[d] = yv[u]; ((uint8_t*)op)[d] = pv[u];
+        } else {
+          copy_elem(ox, x, xs, d, i);
+          copy_elem(oy, y, ys, d, i);
+          copy_elem(ot, t, ts, d, i);
+          copy_elem(op, p, ps, d, i);
+        }
+      }
+      __syncwarp();
+    }
   }
 }
 
@@ -876,19 +975,28 @@ extern "C" int egpt_split_time(const void* x, const void* y, const void* t, cons
 
   split_init_kernel<<<1, 1, 0, stream>>>(minmax);
   EGPT_LAUNCH_CHECK();
-  EGPT_CUDA(cudaMemsetAsync(table, 0, table_bytes, stream));
   int blocks = (int)((n_events + 1023) / 1024);
   if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-  split_minmax_kernel<<<blocks, 256, 0, stream>>>(t, t_dtype, n_events, interval, minmax);
+  const bool t64 = dtype_size(t_dtype) == 8;
+  const bool fast = t64 && dtype_size(x_dtype) == 2 && dtype_size(y_dtype) == 2 && dtype_size(p_dtype) == 1;
+  if (t64) split_minmax_kernel<true><<<blocks, 256, 0, stream>>>(t, t_dtype, n_events, minmax);
+  else split_minmax_kernel<false><<<blocks, 256, 0, stream>>>(t, t_dtype, n_events, minmax);
   EGPT_LAUNCH_CHECK();
   const int warps_per_cta = 4;
   const int cblocks = (pl.n_chunks + warps_per_cta - 1) / warps_per_cta;
-  split_count_kernel<<<cblocks, warps_per_cta * 32, 0, stream>>>(t, t_dtype, pl, interval, minmax, table, status);
+  if (t64) split_count_kernel<true><<<cblocks, warps_per_cta * 32, 0, stream>>>(t, t_dtype, pl, interval, minmax, table, status);
+  else split_count_kernel<false><<<cblocks, warps_per_cta * 32, 0, stream>>>(t, t_dtype, pl, interval, minmax, table, status);
   EGPT_LAUNCH_CHECK();
-  split_scan_kernel<<<1, 1024, 0, stream>>>(pl, minmax, table, bin_start, out_offsets, out_nwindows, max_windows);
+  split_column_scan_kernel<<<max_windows < 4 * kNumSMs ? max_windows : 4 * kNumSMs, 256, 0, stream>>>(pl, interval, minmax, table, bin_start);
   EGPT_LAUNCH_CHECK();
-  split_scatter_kernel<<<cblocks, warps_per_cta * 32, 0, stream>>>(x, y, t, p, dtype_size(x_dtype), dtype_size(y_dtype),
-      t_dtype, dtype_size(p_dtype), pl, interval, minmax, table, out_x, out_y, out_t, out_p);
+  split_bin_scan_kernel<<<1, 1024, 0, stream>>>(pl, interval, minmax, bin_start, out_offsets, out_nwindows, max_windows);
+  EGPT_LAUNCH_CHECK();
+  if (fast)
+    split_scatter_kernel<true><<<cblocks, warps_per_cta * 32, 0, stream>>>(x, y, t, p, 2, 2, t_dtype, 1, pl, interval, minmax, table,
+                                                                          bin_start, out_x, out_y, out_t, out_p);
+  else
+    split_scatter_kernel<false><<<cblocks, warps_per_cta * 32, 0, stream>>>(x, y, t, p, dtype_size(x_dtype), dtype_size(y_dtype),
+        t_dtype, dtype_size(p_dtype), pl, interval, minmax, table, bin_start, out_x, out_y, out_t, out_p);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
 }

@@ -48,7 +48,7 @@ typedef enum {
 enum {
   EGPT_FLAG_EMPTY_SLICE = 1,   /* a frame slice has no events: the reference raises ValueError    */
   EGPT_FLAG_OUT_OF_RANGE = 2,  /* x >= W, y >= H or a negative coordinate                         */
-  EGPT_FLAG_TOO_MANY_BINS = 4, /* split: more distinct time bins than max_windows                 */
+  EGPT_FLAG_TOO_MANY_BINS = 4, /* split: the bins between the first and last event exceed max_windows */
   EGPT_FLAG_FILTER_TOO_WIDE = 8 /* preprocess: down-scale needs more filter taps than EGPT_MAX_TAPS */
 };
 
@@ -77,6 +77,9 @@ int egpt_version(void);
 /* Stable partition of a stream into time bins  bin = floor(t / interval);  bins ascending,     */
 /* empty bins skipped, event order inside a bin preserved, t need not be sorted.  Outputs are   */
 /* the permuted x,y,t,p (same dtypes, n elements), out_offsets[0..n_windows] and *out_nwindows. */
+/* max_windows bounds the SPAN of bins, floor(t_max/interval) - floor(t_min/interval) + 1, empty  */
+/* bins included (the scratch table is chunks x span); beyond it EGPT_FLAG_TOO_MANY_BINS is set   */
+/* and no window is returned -- call again with max_windows >= span (the Python mirror does).     */
 size_t egpt_split_time_workspace_bytes(int64_t n_events, int max_windows);
 int egpt_split_time(const void* x, const void* y, const void* t, const void* p,
                     int x_dtype, int y_dtype, int t_dtype, int p_dtype,

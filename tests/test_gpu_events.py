@@ -222,8 +222,24 @@ def test_split_dsec_window_and_large_sorted_stream(dev):
         for g, w in zip(got, want):
             for k in "xytp":
                 assert np.array_equal(g[k], w[k])
-    with pytest.raises(ValueError):       # 50 ms / 7 us = 7143 bins > max_windows: reported, not silently truncated
-        common.split_event_by_time(ev, 7, max_windows=4096)
+    # 50 ms / 7 us = 7143 bins > max_windows: the C ABI reports EGPT_FLAG_TOO_MANY_BINS (never a silent truncation) and the
+    # mirror splits again with the span the stream needs -- the reference's result either way (np.unique has no limit)
+    from eventgpt_b200 import events as E, _lib
+    td = E.to_device(ev["t"], dev)
+    xd, yd, pd = _dev_events(ev, dev)
+    out = E.split_time(xd, yd, td, pd, 7, 4096)
+    assert int(out[6].item()) & _lib.FLAG_TOO_MANY_BINS and int(out[5].item()) == 0
+    got = common.split_event_by_time(ev, 7, max_windows=4096)
+    want = oev.split_event_by_time(ev, 7)
+    assert len(got) == len(want) > 4096
+    for g, w in zip(got[:50] + got[-50:], want[:50] + want[-50:]):
+        for k in "xytp":
+            assert np.array_equal(g[k], w[k])
+    # two bursts 300 s apart (a recording with a gap): 2 windows, 6001 bins of span
+    gap = {k: np.concatenate([ev[k][:1000], ev[k][-1000:]]) for k in "xytp"}
+    gap["t"] = np.concatenate([ev["t"][:1000], ev["t"][-1000:] + 300_000_000])
+    got, want = common.split_event_by_time(gap, 50000), oev.split_event_by_time(gap, 50000)
+    assert len(got) == len(want) and all(np.array_equal(g[k], w[k]) for g, w in zip(got, want) for k in "xytp")
     rng = np.random.default_rng(9)
     n = 3_000_000
     st = dict(t=np.sort(rng.integers(0, 1_000_000, n)).astype(np.int64), x=rng.integers(0, 640, n).astype(np.uint16),
