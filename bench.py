@@ -240,6 +240,17 @@ def run_ours(args, rank, world, local_rank):
 
     fe = EventGPTVisualFrontEnd(random_state_dict(0, 24), dev, num_layers=24)
     dx, dy, dp = (t.to(dev) for t in (hx, hy, hp))
+    dts = None
+    if args.ingest:
+        # --ingest: every chunk arrives as ONE time-ordered stream (int64 microseconds, window i covers
+        # [i*50 ms, (i+1)*50 ms)) and is cut into its windows on the device by egpt_split_time (common/common.py:76-107)
+        # inside the step; the window offsets then come from the split, not from the host
+        from eventgpt_b200 import events as E
+        rng = np.random.default_rng([7, rank])
+        dts = []
+        for b, e in chunks:
+            t = np.concatenate([np.sort(rng.integers(i * 50_000, (i + 1) * 50_000, EV)) for i in range(e - b)]).astype(np.int64)
+            dts.append(torch.from_numpy(t + 1_700_000_000_000_000).to(dev))
     doffs = [h.to(dev) for h in hoffs]
     # two token / gather buffer pairs: with more than one GPU the final all_gather of step i runs on NCCL's stream while step
     # i+1 computes (the hot path itself has no collective; the gather only delivers the result)
@@ -264,7 +275,11 @@ def run_ours(args, rank, world, local_rank):
         if pending[k] is not None:
             pending[k].wait()                         # the gather that last read tokens[k] has finished
             pending[k] = None
-        for (b, e), doff in zip(chunks, doffs):
+        for ci, ((b, e), doff) in enumerate(zip(chunks, doffs)):
+            if dts is not None:
+                sx, sy, _, sp, soff, _, _ = E.split_time(dx[b * EV:e * EV], dy[b * EV:e * EV], dts[ci], dp[b * EV:e * EV], 50_000, 64)
+                fe.visual_tokens(sx, sy, sp, soff[:e - b + 1], (H, W), out=tokens[k][b:e], check_flags=False)
+                continue
             fe.visual_tokens(dx[b * EV:e * EV], dy[b * EV:e * EV], dp[b * EV:e * EV], doff, (H, W), out=tokens[k][b:e],
                              check_flags=False)
             if splice_in is not None:
@@ -365,6 +380,8 @@ def run_ours(args, rank, world, local_rank):
             "data": "synthetic",
             "config": {"workload": cfg["workload"], "windows_per_gpu": n_local, "windows_total": B_total, "events_per_window": EV,
                        "windows_per_library_call": cmax,
+                       "ingest": "each chunk is one time-ordered int64 stream, cut into windows by egpt_split_time inside the step"
+                                 if args.ingest else "window offsets given (the reference's per-window .npy files)",
                        "sensor": [H, W], "frames_per_window": N_FRAMES, "weights": "random-init CLIP ViT-L/14-336 + projector + adaptor",
                        "parallelism": f"dp{world} (windows sharded, final all_gather of tokens overlapped with the next step)" if world > 1 else "dp1",
                        "l2": "per-step working set (~4 GB of activations, >= 160 MB of events) exceeds the 126 MB L2"},
@@ -457,6 +474,8 @@ def main():
     ap.add_argument("--config", type=int, default=1, choices=[1, 2, 3, 4],
                     help="index into BASELINE.json configs (1 = the driver's default; 3 = raster-only sweep)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ingest", action="store_true",
+                    help="device-resident arm only: cut each chunk's time-ordered stream into windows with egpt_split_time inside the step")
     ap.add_argument("--raster-worker", default=None, help=argparse.SUPPRESS)
     args = ap.parse_args()
     if args.raster_worker:
