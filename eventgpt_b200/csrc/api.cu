@@ -34,24 +34,31 @@ void prof_end(cudaStream_t stream) {
 }
 
 // kernels implemented in the other translation units
-int gemm_bf16(const void* A, const void* B, const float* bias, void* out, long long M, int N, int K, int epilogue, cudaStream_t);
+int gemm_bf16(const void* A, const void* B, const float* bias, void* out, long long M, int N, int K, int epilogue, cudaStream_t,
+              void* out2 = nullptr, const float* colsum = nullptr, float* stats = nullptr);
+int ln_fold(void* w, const float* gamma, const float* beta, const float* bias, float* colsum, float* bias_out, int N, int K, cudaStream_t);
 int attention(const void* qkv, int n_frames_total, void* out, cudaStream_t);
 int layernorm_bf16(const float* h, const float* gamma, const float* beta, void* y, long long rows, cudaStream_t);
-int embed_preln(const float* patch, const float* cls, const float* pos, const float* gamma, const float* beta, float* h, long long rows, cudaStream_t);
+int embed_preln(const float* patch, const float* cls, const float* pos, const float* gamma, const float* beta, float* h, void* hb,
+                float* stats, long long rows, cudaStream_t);
 int f32_to_bf16(const float* in, void* out, long long n, cudaStream_t);
 int im2col(const uint16_t* pix, uint16_t* patches, int F, cudaStream_t);
 int scale_bf16(const void* in, void* out, float scale, long long n, cudaStream_t);
 int scale_f32(const float* in, float* out, float scale, long long n, cudaStream_t);
 int pad_patch_weight(const void* in, void* out, cudaStream_t);
 
-enum { EPI_BIAS_BF16 = 0, EPI_QUICKGELU_BF16 = 1, EPI_GELU_BF16 = 2, EPI_RESIDUAL_F32 = 3, EPI_STORE_F32 = 4 };
+enum { EPI_BIAS_BF16 = 0, EPI_QUICKGELU_BF16 = 1, EPI_GELU_BF16 = 2, EPI_RESIDUAL_F32 = 3, EPI_STORE_F32 = 4,
+       EPI_RESIDUAL_LN = 5, EPI_LN_BIAS_BF16 = 6, EPI_LN_QUICKGELU_BF16 = 7 };
 
 constexpr int kHid = EGPT_HIDDEN, kTok = EGPT_TOKENS, kLlm = EGPT_LLM_HIDDEN, kMlp = 4096, kPatchK = 640;
 
+// layer_norm1 / layer_norm2 are folded into qkv / fc1 at set-up: qkv_w, fc1_w hold gamma . W, qkv_b, fc1_b hold
+// beta W^T + b, qkv_c, fc1_c the column sums of the folded weights (see ln_fold_kernel)
 struct Layer {
   float *ln1_w, *ln1_b, *ln2_w, *ln2_b;
   uint16_t *qkv_w, *o_w, *fc1_w, *fc2_w;
   float *qkv_b, *o_b, *fc1_b, *fc2_b;
+  float *qkv_c, *fc1_c;
 };
 
 }  // namespace egpt
@@ -78,7 +85,8 @@ struct SlabPlan {
 // workspace layout of the tower / projector stage for F frames
 struct TowerWs {
   float* h;          // [M,1024] fp32 residual stream
-  uint16_t* y;       // [M,1024] bf16 (LayerNorm output / bf16 hidden)
+  uint16_t* y;       // [M,1024] bf16 copy of the residual stream (A operand of the LayerNorm-folding GEMMs)
+  float* stats;      // [M,4,2] per-row sum / sum of squares of h, one pair per 256-column tile
   uint16_t* qkv;     // [M,3072] bf16        (aliases: im2col patches [Mp,640])
   uint16_t* attn;    // [M,1024] bf16
   uint16_t* mlp;     // [M,4096] bf16        (aliases: patch GEMM output fp32 [Mp,1024])
@@ -99,6 +107,7 @@ static size_t tower_ws_bytes(int F) {
   b += align_up(M * kLlm * 2, 1024);
   b += align_up((size_t)F * (8 + kTok) * kLlm * 2, 1024);          // pooled (n_frames >= 1 per window)
   b += align_up((size_t)F * 32 * kLlm * 4, 1024);                  // pooling partial sums
+  b += align_up(M * 8 * 4, 1024);                                  // LayerNorm statistics
   return b + 16 * 1024;
 }
 
@@ -114,6 +123,7 @@ static bool carve_tower_ws(void* ws, size_t bytes, int F, TowerWs* o) {
   o->pooled = (uint16_t*)a.take((size_t)F * (8 + kTok) * kLlm * 2);
   o->pool_partial_bytes = (size_t)F * 32 * kLlm * 4;
   o->pool_partial = (float*)a.take(o->pool_partial_bytes);
+  o->stats = (float*)a.take(M * 8 * 4);
   return a.ok();
 }
 
@@ -122,16 +132,17 @@ static int run_tower_from_patches(egpt_handle* hd, int F, TowerWs& w, cudaStream
   const long long M = (long long)F * kTok, Mp = (long long)F * (kTok - 1);
   float* patch_out = reinterpret_cast<float*>(w.mlp);
   EGPT_TRY(gemm_bf16(w.qkv, hd->patch_w, nullptr, patch_out, Mp, kHid, kPatchK, EPI_STORE_F32, st));
-  EGPT_TRY(embed_preln(patch_out, hd->cls, hd->pos, hd->pre_w, hd->pre_b, w.h, M, st));
+  EGPT_TRY(embed_preln(patch_out, hd->cls, hd->pos, hd->pre_w, hd->pre_b, w.h, w.y, w.stats, M, st));
+  // Per layer (transformers CLIPEncoderLayer): the two LayerNorms never run as passes of their own.  Each residual GEMM
+  // (out-proj, fc2) leaves the new h in fp32, a bf16 copy of it in y and the row sums in stats; the GEMM that consumes
+  // LayerNorm(h) (qkv, fc1) multiplies the bf16 copy by gamma . W and normalises in its epilogue.
   for (int l = 0; l < hd->num_layers; ++l) {
     const Layer& L = hd->layers[l];
-    EGPT_TRY(layernorm_bf16(w.h, L.ln1_w, L.ln1_b, w.y, M, st));
-    EGPT_TRY(gemm_bf16(w.y, L.qkv_w, L.qkv_b, w.qkv, M, 3 * kHid, kHid, EPI_BIAS_BF16, st));
+    EGPT_TRY(gemm_bf16(w.y, L.qkv_w, L.qkv_b, w.qkv, M, 3 * kHid, kHid, EPI_LN_BIAS_BF16, st, nullptr, L.qkv_c, w.stats));
     EGPT_TRY(attention(w.qkv, F, w.attn, st));
-    EGPT_TRY(gemm_bf16(w.attn, L.o_w, L.o_b, w.h, M, kHid, kHid, EPI_RESIDUAL_F32, st));
-    EGPT_TRY(layernorm_bf16(w.h, L.ln2_w, L.ln2_b, w.y, M, st));
-    EGPT_TRY(gemm_bf16(w.y, L.fc1_w, L.fc1_b, w.mlp, M, kMlp, kHid, EPI_QUICKGELU_BF16, st));
-    EGPT_TRY(gemm_bf16(w.mlp, L.fc2_w, L.fc2_b, w.h, M, kHid, kMlp, EPI_RESIDUAL_F32, st));
+    EGPT_TRY(gemm_bf16(w.attn, L.o_w, L.o_b, w.h, M, kHid, kHid, EPI_RESIDUAL_LN, st, w.y, nullptr, w.stats));
+    EGPT_TRY(gemm_bf16(w.y, L.fc1_w, L.fc1_b, w.mlp, M, kMlp, kHid, EPI_LN_QUICKGELU_BF16, st, nullptr, L.fc1_c, w.stats));
+    EGPT_TRY(gemm_bf16(w.mlp, L.fc2_w, L.fc2_b, w.h, M, kHid, kMlp, EPI_RESIDUAL_LN, st, w.y, nullptr, w.stats));
   }
   return EGPT_OK;
 }
@@ -139,7 +150,7 @@ static int run_tower_from_patches(egpt_handle* hd, int F, TowerWs& w, cudaStream
 // ws.h (fp32 last_hidden_state) -> visual_projector -> dst bf16 [M,4096]
 static int run_projector(egpt_handle* hd, int F, TowerWs& w, uint16_t* dst, cudaStream_t st) {
   const long long M = (long long)F * kTok;
-  EGPT_TRY(f32_to_bf16(w.h, w.y, M * kHid, st));
+  // ws.y already holds the bf16 copy of the last hidden state (written by the last residual GEMM)
   EGPT_TRY(gemm_bf16(w.y, hd->proj0_w, hd->proj0_b, w.mlp, M, kLlm, kHid, EPI_GELU_BF16, st));
   EGPT_TRY(gemm_bf16(w.mlp, hd->proj2_w, hd->proj2_b, dst, M, kLlm, kLlm, EPI_BIAS_BF16, st));
   return EGPT_OK;
@@ -150,14 +161,11 @@ static int run_projector(egpt_handle* hd, int F, TowerWs& w, uint16_t* dst, cuda
 // The projector is Linear -> GELU -> Linear and the pooling is a mean, so the second Linear (affine) commutes with it:
 //   pool(W2 g + b2) = W2 pool(g) + b2.  Pooling the GELU output first shrinks the second projector GEMM from
 // n*577 to n+577 rows per window (5x fewer at n = 5); the adaptor then runs on the same pooled rows.
-// hidden == nullptr: the last hidden state is the fp32 residual stream in ws.h (cast to bf16 first); otherwise bf16 [M,1024]
+// hidden == nullptr: the last hidden state is what the tower left in ws.y; otherwise bf16 [M,1024] from the caller
 static int run_projector_pool_adaptor(egpt_handle* hd, int B, int n, TowerWs& w, uint16_t* out_tokens, cudaStream_t st,
                                       const uint16_t* hidden = nullptr) {
   const long long M = (long long)B * n * kTok, Mo = (long long)B * (n + kTok);
-  if (hidden == nullptr) {
-    EGPT_TRY(f32_to_bf16(w.h, w.y, M * kHid, st));
-    hidden = w.y;
-  }
+  if (hidden == nullptr) hidden = w.y;       // the bf16 copy of the last hidden state, written by the last residual GEMM
   EGPT_TRY(gemm_bf16(hidden, hd->proj0_w, hd->proj0_b, w.mlp, M, kLlm, kHid, EPI_GELU_BF16, st));
   EGPT_TRY(egpt_spatio_temporal_pool(w.mlp, 0, B, n, kTok, kLlm, n, w.pooled, w.pool_partial, w.pool_partial_bytes, st));
   EGPT_TRY(gemm_bf16(w.pooled, hd->proj2_w, hd->proj2_b, w.z, Mo, kLlm, kLlm, EPI_BIAS_BF16, st));
@@ -213,13 +221,14 @@ extern "C" int egpt_create(const egpt_weights* wh, int device, egpt_handle** out
   SlabPlan p;
   const size_t o_cls = p.take(kHid * 4), o_pos = p.take((size_t)kTok * kHid * 4), o_prew = p.take(kHid * 4),
                o_preb = p.take(kHid * 4), o_patch = p.take((size_t)kHid * kPatchK * 2);
-  struct LOff { size_t ln1w, ln1b, ln2w, ln2b, qkvw, ow, fc1w, fc2w, qkvb, ob, fc1b, fc2b; };
+  struct LOff { size_t ln1w, ln1b, ln2w, ln2b, qkvw, ow, fc1w, fc2w, qkvb, ob, fc1b, fc2b, qkvc, fc1c; };
   std::vector<LOff> lo(L);
   for (int l = 0; l < L; ++l) {
     lo[l].ln1w = p.take(kHid * 4); lo[l].ln1b = p.take(kHid * 4); lo[l].ln2w = p.take(kHid * 4); lo[l].ln2b = p.take(kHid * 4);
     lo[l].qkvw = p.take((size_t)3 * kHid * kHid * 2); lo[l].ow = p.take((size_t)kHid * kHid * 2);
     lo[l].fc1w = p.take((size_t)kMlp * kHid * 2); lo[l].fc2w = p.take((size_t)kHid * kMlp * 2);
     lo[l].qkvb = p.take(3 * kHid * 4); lo[l].ob = p.take(kHid * 4); lo[l].fc1b = p.take(kMlp * 4); lo[l].fc2b = p.take(kHid * 4);
+    lo[l].qkvc = p.take(3 * kHid * 4); lo[l].fc1c = p.take(kMlp * 4);
   }
   const size_t o_p0w = p.take((size_t)kLlm * kHid * 2), o_p0b = p.take(kLlm * 4), o_p2w = p.take((size_t)kLlm * kLlm * 2),
                o_p2b = p.take(kLlm * 4), o_aw = p.take((size_t)kLlm * kLlm * 2), o_ab = p.take(kLlm * 4);
@@ -259,6 +268,10 @@ extern "C" int egpt_create(const egpt_weights* wh, int device, egpt_handle** out
     Lr.ln1_w = (float*)(s + lo[l].ln1w); Lr.ln1_b = (float*)(s + lo[l].ln1b); Lr.ln2_w = (float*)(s + lo[l].ln2w); Lr.ln2_b = (float*)(s + lo[l].ln2b);
     Lr.qkv_w = (uint16_t*)(s + lo[l].qkvw); Lr.o_w = (uint16_t*)(s + lo[l].ow); Lr.fc1_w = (uint16_t*)(s + lo[l].fc1w); Lr.fc2_w = (uint16_t*)(s + lo[l].fc2w);
     Lr.qkv_b = (float*)(s + lo[l].qkvb); Lr.o_b = (float*)(s + lo[l].ob); Lr.fc1_b = (float*)(s + lo[l].fc1b); Lr.fc2_b = (float*)(s + lo[l].fc2b);
+    Lr.qkv_c = (float*)(s + lo[l].qkvc); Lr.fc1_c = (float*)(s + lo[l].fc1c);
+    // fold layer_norm1 into the packed qkv projection and layer_norm2 into fc1 (in place, after the copies above)
+    if (rc == EGPT_OK) rc = ln_fold(Lr.qkv_w, Lr.ln1_w, Lr.ln1_b, Lr.qkv_b, Lr.qkv_c, Lr.qkv_b, 3 * kHid, kHid, st);
+    if (rc == EGPT_OK) rc = ln_fold(Lr.fc1_w, Lr.ln2_w, Lr.ln2_b, Lr.fc1_b, Lr.fc1_c, Lr.fc1_b, kMlp, kHid, st);
   }
   cp(o_p0w, wh->proj0_w, (size_t)kLlm * kHid * 2); cp(o_p0b, wh->proj0_b, kLlm * 4);
   cp(o_p2w, wh->proj2_w, (size_t)kLlm * kLlm * 2); cp(o_p2b, wh->proj2_b, kLlm * 4);
@@ -307,7 +320,7 @@ extern "C" int egpt_tower(egpt_handle* h, const uint16_t* pixel_values, int F, u
   EGPT_WS_OR_FAIL(F);
   EGPT_TRY(im2col(pixel_values, w.qkv, F, st));
   EGPT_TRY(run_tower_from_patches(h, F, w, st));
-  EGPT_TRY(f32_to_bf16(w.h, out_hidden, (long long)F * kTok * kHid, st));
+  EGPT_CUDA(cudaMemcpyAsync(out_hidden, w.y, (size_t)F * kTok * kHid * 2, cudaMemcpyDeviceToDevice, st));
   return EGPT_OK;
 }
 

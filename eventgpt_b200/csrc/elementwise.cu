@@ -73,7 +73,7 @@ layernorm_bf16_kernel(const float* __restrict__ h, const float* __restrict__ gam
 __global__ void __launch_bounds__(256)
 embed_preln_kernel(const float* __restrict__ patch, const float* __restrict__ cls, const float* __restrict__ pos,
                    const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ h,
-                   long long rows) {
+                   __nv_bfloat16* __restrict__ hb, float* __restrict__ stats, long long rows) {
   const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= rows) return;
@@ -90,6 +90,44 @@ embed_preln_kernel(const float* __restrict__ patch, const float* __restrict__ cl
     x[4 * c] = v.x + p.x; x[4 * c + 1] = v.y + p.y; x[4 * c + 2] = v.z + p.z; x[4 * c + 3] = v.w + p.w;
   }
   ln_row<false>(x, gamma, beta, lane, h + row * kHid);
+  // what the first encoder layer's LayerNorm-folding GEMM needs: a bf16 copy of the row and its sum / sum of squares
+  // (ln_row left the row in h; every lane re-reads the 32 values it wrote)
+  __syncwarp();
+  float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    const int col = c * 128 + lane * 4;
+    const float4 v = *reinterpret_cast<const float4*>(h + row * kHid + col);
+    s1 += (v.x + v.y) + (v.z + v.w);
+    s2 = fmaf(v.x, v.x, fmaf(v.y, v.y, fmaf(v.z, v.z, fmaf(v.w, v.w, s2))));
+    *reinterpret_cast<uint2*>(hb + row * kHid + col) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+  }
+  s1 = warp_sum(s1);
+  s2 = warp_sum(s2);
+  if (lane < 4) *reinterpret_cast<float2*>(stats + row * 8 + 2 * lane) = lane == 0 ? make_float2(s1, s2) : make_float2(0.f, 0.f);
+}
+
+// LayerNorm folded into the linear layer that follows it (model set-up, once per layer):
+//   LN(h) W^T + b = rstd * (h (gamma . W)^T - mean * colsum) + (beta W^T + b),  colsum_n = sum_k (gamma . W)_nk
+// w [N, K] bf16 is overwritten with bf16(gamma_k * w_nk); colsum is taken over the ROUNDED products (what the tensor
+// cores will multiply), bias_out over the original weights.  One warp per output row.
+__global__ void __launch_bounds__(256)
+ln_fold_kernel(__nv_bfloat16* __restrict__ w, const float* __restrict__ gamma, const float* __restrict__ beta,
+               const float* __restrict__ bias, float* __restrict__ colsum, float* __restrict__ bias_out, int N, int K) {
+  const int n = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (n >= N) return;
+  __nv_bfloat16* row = w + (size_t)n * K;
+  float c = 0.f, d = 0.f;
+  for (int k = lane; k < K; k += 32) {
+    const float wv = __bfloat162float(row[k]);
+    const __nv_bfloat16 f = __float2bfloat16_rn(gamma[k] * wv);
+    row[k] = f;
+    c += __bfloat162float(f);
+    d = fmaf(beta[k], wv, d);
+  }
+  c = warp_sum(c);
+  d = warp_sum(d);
+  if (lane == 0) { colsum[n] = c; bias_out[n] = d + bias[n]; }
 }
 
 // fp32 -> bf16, 8 elements per thread
@@ -285,9 +323,15 @@ int layernorm_bf16(const float* h, const float* gamma, const float* beta, void* 
   return EGPT_OK;
 }
 int embed_preln(const float* patch, const float* cls, const float* pos, const float* gamma, const float* beta, float* h,
-                long long rows, cudaStream_t st) {
-  ProfScope prof(PROF_ELEMENTWISE, (double)rows * kHid * 8, st);
-  embed_preln_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(patch, cls, pos, gamma, beta, h, rows);
+                void* hb, float* stats, long long rows, cudaStream_t st) {
+  ProfScope prof(PROF_ELEMENTWISE, (double)rows * kHid * 10, st);
+  embed_preln_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(patch, cls, pos, gamma, beta, h, (__nv_bfloat16*)hb, stats, rows);
+  EGPT_LAUNCH_CHECK();
+  return EGPT_OK;
+}
+int ln_fold(void* w, const float* gamma, const float* beta, const float* bias, float* colsum, float* bias_out, int N, int K,
+            cudaStream_t st) {
+  ln_fold_kernel<<<(N + 7) / 8, 256, 0, st>>>((__nv_bfloat16*)w, gamma, beta, bias, colsum, bias_out, N, K);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
 }

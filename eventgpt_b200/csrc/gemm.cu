@@ -34,7 +34,14 @@ constexpr int kTmemCols = 2 * BN;                  // two accumulator stages
 constexpr int kGemmThreads = 256;
 constexpr int kStagingBytes = 4 * 2 * 4096;        // 4 epilogue warps x 2 buffers x (32 rows x 128 B)
 
-enum { EPI_BIAS_BF16 = 0, EPI_QUICKGELU_BF16 = 1, EPI_GELU_BF16 = 2, EPI_RESIDUAL_F32 = 3, EPI_STORE_F32 = 4 };
+enum { EPI_BIAS_BF16 = 0, EPI_QUICKGELU_BF16 = 1, EPI_GELU_BF16 = 2, EPI_RESIDUAL_F32 = 3, EPI_STORE_F32 = 4,
+       // LayerNorm folded into the two GEMMs around it (the separate LayerNorm pass over the residual stream disappears):
+       // 5: producer of the residual stream: h = h + acc + bias read-add-stored through shared memory, a bf16 copy of the new
+       //    h (the A operand of the next GEMM) and the per-row sum / sum of squares of this tile's 256 columns;
+       // 6, 7: consumer of LayerNorm(h): A is the bf16 copy of h itself, B holds gamma (.) W, and the epilogue applies
+       //    rstd * (acc - mean * colsum) + bias' per row (mean, rstd from the four column tiles' partial sums);  7 adds QuickGELU
+       EPI_RESIDUAL_LN = 5, EPI_LN_BIAS_BF16 = 6, EPI_LN_QUICKGELU_BF16 = 7 };
+constexpr float kLnEpsG = 1e-5f;
 
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
@@ -43,7 +50,7 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 
 template <int EPI>
 __device__ __forceinline__ float activate(float v) {
-  if (EPI == EPI_QUICKGELU_BF16) {
+  if (EPI == EPI_QUICKGELU_BF16 || EPI == EPI_LN_QUICKGELU_BF16) {
     // x * sigmoid(1.702 x) with sigmoid(z) = 0.5 + 0.5 tanh(z/2): one MUFU op, no division
     float t;
     asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.851f * v));
@@ -59,23 +66,30 @@ __device__ __forceinline__ float activate(float v) {
 // 48 KB -> six stages fit where four did, and the L2 -> SM operand traffic drops by a third.  The leader
 // CTA issues the MMAs; full barriers live in the leader (both CTAs' TMA bytes are credited to them), empty /
 // accumulator-ready barriers are multicast to both CTAs; each CTA drains its own 128 accumulator rows.
-constexpr int kStages2 = 6;
 constexpr int kBHalfBytes = (BN / 2) * BK * 2;          // 16 KB
 constexpr int kStageBytes2 = kABytes + kBHalfBytes;     // 32 KB per CTA
-constexpr int kGemmSmem2 = kStages2 * kStageBytes2 + kStagingBytes + 1024 + 256;
+// the residual + LayerNorm-statistics epilogue stages a bf16 copy next to the fp32 tile: one operand stage less
+constexpr int stages_of(int epi) { return epi == EPI_RESIDUAL_LN ? 5 : 6; }
+constexpr int extra_staging_of(int epi) { return epi == EPI_RESIDUAL_LN ? 4 * 2 * 4096 : 0; }
+constexpr int gemm_smem_of(int epi) { return stages_of(epi) * kStageBytes2 + kStagingBytes + extra_staging_of(epi) + 1024 + 256; }
 
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                  const __grid_constant__ CUtensorMap tmap_out, const float* __restrict__ bias, long long M, int N, int K) {
+                  const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_out2,
+                  const float* __restrict__ bias, const float* __restrict__ colsum, float* __restrict__ stats,
+                  long long M, int N, int K) {
+  constexpr int kStages2 = stages_of(EPI);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* staging = smem + kStages2 * kStageBytes2;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + kStagingBytes);
+  uint8_t* staging2 = staging + kStagingBytes;                           // bf16 copy (EPI_RESIDUAL_LN only)
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging2 + extra_staging_of(EPI));
   uint64_t* empty_bar = full_bar + kStages2;
   uint64_t* tmem_full = empty_bar + kStages2;
   uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* ld_bar = tmem_empty + 2;                                     // [4 warps][2 buffers]: residual tile loads
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(ld_bar + 8);
 
   // warp index and CTA rank are made warp-uniform by construction: the producer and MMA warps then run their loops with
   // uniform control flow and operands (descriptors, coordinates and barrier addresses in uniform registers) and only the
@@ -93,10 +107,12 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     ptx::prefetch_tensormap(&tmap_a);
     ptx::prefetch_tensormap(&tmap_b);
     ptx::prefetch_tensormap(&tmap_out);
+    if (EPI == EPI_RESIDUAL_LN) ptx::prefetch_tensormap(&tmap_out2);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages2; ++i) { ptx::mbar_init(full_bar + i, 1); ptx::mbar_init(empty_bar + i, 1); }
     for (int i = 0; i < 2; ++i) { ptx::mbar_init(tmem_full + i, 1); ptx::mbar_init(tmem_empty + i, 256); }
+    for (int i = 0; i < 8; ++i) ptx::mbar_init(ld_bar + i, 1);
     ptx::fence_barrier_init();
   }
   if (warp == 2) {
@@ -155,15 +171,40 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   } else if (warp >= 4) {
     // ===== epilogue (both CTAs, own 128 rows) =====
     const int q = warp & 3;
-    constexpr bool kF32Out = (EPI == EPI_RESIDUAL_F32 || EPI == EPI_STORE_F32);
+    constexpr bool kF32Out = (EPI == EPI_RESIDUAL_F32 || EPI == EPI_STORE_F32 || EPI == EPI_RESIDUAL_LN);
+    constexpr bool kLnIn = (EPI == EPI_LN_BIAS_BF16 || EPI == EPI_LN_QUICKGELU_BF16);
     constexpr int CH = kF32Out ? 32 : 64;
     uint8_t* my_stage = staging + q * 8192;
+    uint8_t* my_stage2 = staging2 + q * 8192;
+    uint64_t* my_ld = ld_bar + q * 2;
+    uint32_t ld_phase[2] = {0, 0};
     const uint32_t sw = (uint32_t)(lane & 7);
     const uint32_t leader_tmem_empty = ptx::mapa_u32(tmem_empty, 0);
     int acc = 0; uint32_t acc_phase = 0; int buf = 0;
     for (long long tile = first; tile < num_tiles; tile += step) {
       const int row0 = (int)(tile / n_tiles) * (2 * BM) + (int)rank * BM + q * 32;
       const int n0 = (int)(tile % n_tiles) * BN;
+      float mean = 0.f, rstd = 0.f, s1 = 0.f, s2 = 0.f;
+      if (kLnIn) {
+        // LayerNorm statistics of this lane's row from the partial sums the producing GEMM left (K = row length)
+        const long long r = (long long)row0 + lane;
+        if (r < M) {
+          const float4 a = __ldg(reinterpret_cast<const float4*>(stats + r * 8)), b = __ldg(reinterpret_cast<const float4*>(stats + r * 8) + 1);
+          const float inv = 1.0f / (float)K;
+          mean = ((a.x + a.z) + (b.x + b.z)) * inv;
+          const float var = ((a.y + a.w) + (b.y + b.w)) * inv - mean * mean;
+          rstd = rsqrtf(fmaxf(var, 0.f) + kLnEpsG);
+        }
+      }
+      if (EPI == EPI_RESIDUAL_LN) {
+        // the old residual tile travels into the staging buffer the new one will leave from
+        if (lane == 0) {
+          ptx::bulk_wait_group_read<0>();
+          ptx::mbar_arrive_expect_tx(my_ld + buf, 4096);
+          ptx::tma_load_2d(my_stage + buf * 4096, &tmap_out, my_ld + buf, n0, row0);
+        }
+        __syncwarp();
+      }
       ptx::mbar_wait(tmem_full + acc, acc_phase);
       ptx::tcgen05_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
@@ -177,10 +218,36 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           ptx::tcgen05_fence_before();
           ptx::mbar_arrive_cluster(leader_tmem_empty + (uint32_t)(acc * 8));
         }
-        if (lane == 0) ptx::bulk_wait_group_read<1>();
-        __syncwarp();
+        if (EPI == EPI_RESIDUAL_LN) {
+          // next chunk's residual tile into the other buffer (its last store has been read out), then wait for this one
+          if (lane == 0) {
+            ptx::bulk_wait_group_read<0>();
+            if (c0 + CH < BN) {
+              ptx::mbar_arrive_expect_tx(my_ld + (buf ^ 1), 4096);
+              ptx::tma_load_2d(my_stage + (buf ^ 1) * 4096, &tmap_out, my_ld + (buf ^ 1), n0 + c0 + CH, row0);
+            }
+          }
+          __syncwarp();
+          ptx::mbar_wait(my_ld + buf, ld_phase[buf]);
+          ld_phase[buf] ^= 1;
+        } else {
+          if (lane == 0) ptx::bulk_wait_group_read<1>();
+          __syncwarp();
+        }
         uint8_t* dst = my_stage + buf * 4096 + lane * 128;
-        if (bias != nullptr) {
+        if (kLnIn) {
+          const float4* cp = reinterpret_cast<const float4*>(colsum + n0 + c0);
+          const float4* bp = reinterpret_cast<const float4*>(bias + n0 + c0);
+          const float nm = -mean;
+#pragma unroll
+          for (int j = 0; j < CH / 4; ++j) {
+            const float4 c = __ldg(cp + j), b = __ldg(bp + j);
+            r[4 * j] = __float_as_uint(fmaf(rstd, fmaf(nm, c.x, __uint_as_float(r[4 * j])), b.x));
+            r[4 * j + 1] = __float_as_uint(fmaf(rstd, fmaf(nm, c.y, __uint_as_float(r[4 * j + 1])), b.y));
+            r[4 * j + 2] = __float_as_uint(fmaf(rstd, fmaf(nm, c.z, __uint_as_float(r[4 * j + 2])), b.z));
+            r[4 * j + 3] = __float_as_uint(fmaf(rstd, fmaf(nm, c.w, __uint_as_float(r[4 * j + 3])), b.w));
+          }
+        } else if (bias != nullptr) {
           const float4* bp = reinterpret_cast<const float4*>(bias + n0 + c0);
 #pragma unroll
           for (int j = 0; j < CH / 4; ++j) {
@@ -191,7 +258,31 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             r[4 * j + 3] = __float_as_uint(__uint_as_float(r[4 * j + 3]) + b.w);
           }
         }
-        if (kF32Out) {
+        if (EPI == EPI_RESIDUAL_LN) {
+          // h_new = h_old + acc + bias in place in the staging tile; bf16 copy beside it; running row statistics
+          uint8_t* dst2 = my_stage2 + ((c0 >> 6) & 1) * 4096 + lane * 128;
+          const uint32_t half = (uint32_t)((c0 >> 5) & 1) * 4u;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            uint4* cell = reinterpret_cast<uint4*>(dst + (((uint32_t)j ^ sw) << 4));
+            const uint4 o = *cell;
+            const float v0 = __uint_as_float(o.x) + __uint_as_float(r[4 * j]), v1 = __uint_as_float(o.y) + __uint_as_float(r[4 * j + 1]);
+            const float v2 = __uint_as_float(o.z) + __uint_as_float(r[4 * j + 2]), v3 = __uint_as_float(o.w) + __uint_as_float(r[4 * j + 3]);
+            s1 += (v0 + v1) + (v2 + v3);
+            s2 = fmaf(v0, v0, fmaf(v1, v1, fmaf(v2, v2, fmaf(v3, v3, s2))));
+            *cell = make_uint4(__float_as_uint(v0), __float_as_uint(v1), __float_as_uint(v2), __float_as_uint(v3));
+            r[4 * j] = __float_as_uint(v0); r[4 * j + 1] = __float_as_uint(v1); r[4 * j + 2] = __float_as_uint(v2); r[4 * j + 3] = __float_as_uint(v3);
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 o;
+            o.x = pack_bf16(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
+            o.y = pack_bf16(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+            o.z = pack_bf16(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+            o.w = pack_bf16(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+            *reinterpret_cast<uint4*>(dst2 + (((half + (uint32_t)j) ^ sw) << 4)) = o;
+          }
+        } else if (kF32Out) {
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             *reinterpret_cast<uint4*>(dst + (((uint32_t)j ^ sw) << 4)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
@@ -211,9 +302,15 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         if (lane == 0) {
           if (EPI == EPI_RESIDUAL_F32) ptx::tma_reduce_add_2d(&tmap_out, my_stage + buf * 4096, n0 + c0, row0);
           else ptx::tma_store_2d(&tmap_out, my_stage + buf * 4096, n0 + c0, row0);
+          if (EPI == EPI_RESIDUAL_LN && (c0 & 32))           // two 32-column chunks make one 64-column bf16 tile
+            ptx::tma_store_2d(&tmap_out2, my_stage2 + ((c0 >> 6) & 1) * 4096, n0 + c0 - 32, row0);
           ptx::bulk_commit_group();
         }
         buf ^= 1;
+      }
+      if (EPI == EPI_RESIDUAL_LN) {
+        const long long r = (long long)row0 + lane;
+        if (r < M) *reinterpret_cast<float2*>(stats + r * 8 + 2 * (n0 / BN)) = make_float2(s1, s2);
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
@@ -262,36 +359,48 @@ static int make_tmap(CUtensorMap* map, const void* ptr, bool f32, uint64_t rows,
 }
 
 template <int EPI>
-static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const float* bias,
-                        long long M, int N, int K, cudaStream_t stream) {
+static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& to2,
+                        const float* bias, const float* colsum, float* stats, long long M, int N, int K, cudaStream_t stream) {
   // per launch: the attribute is per device, and one process may drive several GPUs
-  EGPT_CUDA(cudaFuncSetAttribute(gemm2_bf16_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem2));
+  constexpr int smem = gemm_smem_of(EPI);
+  EGPT_CUDA(cudaFuncSetAttribute(gemm2_bf16_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const long long pairs = ((M + 2 * BM - 1) / (2 * BM)) * (N / BN);
   const int grid = (int)(2 * (pairs < kNumSMs / 2 ? pairs : kNumSMs / 2));
-  gemm2_bf16_kernel<EPI><<<grid, kGemmThreads, kGemmSmem2, stream>>>(ta, tb, to, bias, M, N, K);
+  gemm2_bf16_kernel<EPI><<<grid, kGemmThreads, smem, stream>>>(ta, tb, to, to2, bias, colsum, stats, M, N, K);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
 }
 
+// out2 / colsum / stats: only for the LayerNorm-folding epilogues (see the enum)
 int gemm_bf16(const void* A, const void* B, const float* bias, void* out, long long M, int N, int K, int epilogue,
-              cudaStream_t stream) {
+              cudaStream_t stream, void* out2, const float* colsum, float* stats) {
   EGPT_CHECK_ARG(A && B && out, "gemm: null pointer");
   EGPT_CHECK_ARG(M > 0 && N > 0 && K > 0 && N % BN == 0 && K % BK == 0, "gemm: unsupported shape M=%lld N=%d K=%d (N %% 256, K %% 64)",
                  M, N, K);
   EGPT_CHECK_ARG(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
                  (bias == nullptr || (uintptr_t)bias % 16 == 0), "gemm: pointers must be 16-byte aligned");
-  CUtensorMap ta, tb, to;
+  const bool producer = epilogue == EPI_RESIDUAL_LN, consumer = epilogue == EPI_LN_BIAS_BF16 || epilogue == EPI_LN_QUICKGELU_BF16;
+  EGPT_CHECK_ARG(!producer || (N == 4 * BN && out2 && stats && bias && (uintptr_t)out2 % 16 == 0 && (uintptr_t)stats % 32 == 0),
+                 "gemm: the residual + statistics epilogue wants N = 1024, a bf16 copy buffer, a statistics buffer and a bias");
+  EGPT_CHECK_ARG(!consumer || (K == 4 * BN && colsum && stats && bias && (uintptr_t)colsum % 16 == 0 && (uintptr_t)stats % 32 == 0),
+                 "gemm: the LayerNorm-folding epilogue wants K = 1024, column sums, a statistics buffer and a bias");
+  CUtensorMap ta, tb, to, to2;
   ProfScope prof(PROF_GEMM, 2.0 * (double)M * N * K, stream);
-  const bool f32_out = epilogue == EPI_RESIDUAL_F32 || epilogue == EPI_STORE_F32;
+  const bool f32_out = epilogue == EPI_RESIDUAL_F32 || epilogue == EPI_STORE_F32 || producer;
   EGPT_TRY(make_tmap(&ta, A, false, (uint64_t)M, (uint64_t)K, BK, BM));
   EGPT_TRY(make_tmap(&tb, B, false, (uint64_t)N, (uint64_t)K, BK, BN / 2));          // each CTA of a pair loads half of B
   EGPT_TRY(make_tmap(&to, out, f32_out, (uint64_t)M, (uint64_t)N, f32_out ? 32 : 64, 32));
+  if (producer) EGPT_TRY(make_tmap(&to2, out2, false, (uint64_t)M, (uint64_t)N, 64, 32));
+  else to2 = to;
   switch (epilogue) {
-    case EPI_BIAS_BF16: return launch_gemm2<EPI_BIAS_BF16>(ta, tb, to, bias, M, N, K, stream);
-    case EPI_QUICKGELU_BF16: return launch_gemm2<EPI_QUICKGELU_BF16>(ta, tb, to, bias, M, N, K, stream);
-    case EPI_GELU_BF16: return launch_gemm2<EPI_GELU_BF16>(ta, tb, to, bias, M, N, K, stream);
-    case EPI_RESIDUAL_F32: return launch_gemm2<EPI_RESIDUAL_F32>(ta, tb, to, bias, M, N, K, stream);
-    case EPI_STORE_F32: return launch_gemm2<EPI_STORE_F32>(ta, tb, to, bias, M, N, K, stream);
+    case EPI_BIAS_BF16: return launch_gemm2<EPI_BIAS_BF16>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
+    case EPI_QUICKGELU_BF16: return launch_gemm2<EPI_QUICKGELU_BF16>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
+    case EPI_GELU_BF16: return launch_gemm2<EPI_GELU_BF16>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
+    case EPI_RESIDUAL_F32: return launch_gemm2<EPI_RESIDUAL_F32>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
+    case EPI_STORE_F32: return launch_gemm2<EPI_STORE_F32>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
+    case EPI_RESIDUAL_LN: return launch_gemm2<EPI_RESIDUAL_LN>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
+    case EPI_LN_BIAS_BF16: return launch_gemm2<EPI_LN_BIAS_BF16>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
+    case EPI_LN_QUICKGELU_BF16: return launch_gemm2<EPI_LN_QUICKGELU_BF16>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
   }
   set_error("gemm: unknown epilogue %d", epilogue);
   return EGPT_ERR_INVALID;
@@ -301,5 +410,12 @@ int gemm_bf16(const void* A, const void* B, const float* bias, void* out, long l
 
 extern "C" int egpt_gemm_bf16(const uint16_t* A, const uint16_t* B, const float* bias, void* out, int64_t M, int N,
                               int K, int epilogue, void* stream) {
-  return egpt::gemm_bf16(A, B, bias, out, M, N, K, epilogue, (cudaStream_t)stream);
+  EGPT_CHECK_ARG(epilogue >= 0 && epilogue <= egpt::EPI_STORE_F32, "egpt_gemm_bf16: epilogue %d (0..4)", epilogue);
+  return egpt::gemm_bf16(A, B, bias, out, M, N, K, epilogue, (cudaStream_t)stream, nullptr, nullptr, nullptr);
+}
+
+// the LayerNorm-folding epilogues, exposed for tests: 5 needs out2 (bf16 copy) + stats, 6 / 7 need colsum + stats
+extern "C" int egpt_gemm_bf16_ln(const uint16_t* A, const uint16_t* B, const float* bias, void* out, int64_t M, int N,
+                                 int K, int epilogue, void* out2, const float* colsum, float* stats, void* stream) {
+  return egpt::gemm_bf16(A, B, bias, out, M, N, K, epilogue, (cudaStream_t)stream, out2, colsum, stats);
 }
