@@ -32,7 +32,6 @@ constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16;
 constexpr int kABytes = BM * BK * 2;               // 16 KB
 constexpr int kTmemCols = 2 * BN;                  // two accumulator stages
 constexpr int kGemmThreads = 256;
-constexpr int kStagingBytes = 4 * 2 * 4096;        // 4 epilogue warps x 2 buffers x (32 rows x 128 B)
 
 enum { EPI_BIAS_BF16 = 0, EPI_QUICKGELU_BF16 = 1, EPI_GELU_BF16 = 2, EPI_RESIDUAL_F32 = 3, EPI_STORE_F32 = 4,
        // LayerNorm folded into the two GEMMs around it (the separate LayerNorm pass over the residual stream disappears):
@@ -69,9 +68,14 @@ __device__ __forceinline__ float activate(float v) {
 constexpr int kBHalfBytes = (BN / 2) * BK * 2;          // 16 KB
 constexpr int kStageBytes2 = kABytes + kBHalfBytes;     // 32 KB per CTA
 // the residual + LayerNorm-statistics epilogue stages a bf16 copy next to the fp32 tile: one operand stage less
-constexpr int stages_of(int epi) { return epi == EPI_RESIDUAL_LN ? 5 : 6; }
+// the residual + LayerNorm-statistics epilogue keeps four fp32 staging tiles per warp in flight (the old residual tile is
+// fetched three chunks ahead) and stages a bf16 copy beside them: two operand stages less
+constexpr int stages_of(int epi) { return epi == EPI_RESIDUAL_LN ? 4 : 6; }
+constexpr int fbufs_of(int epi) { return epi == EPI_RESIDUAL_LN ? 4 : 2; }          // fp32 / bf16 staging tiles (4 KB) per warp
+constexpr int staging_of(int epi) { return 4 * fbufs_of(epi) * 4096; }
 constexpr int extra_staging_of(int epi) { return epi == EPI_RESIDUAL_LN ? 4 * 2 * 4096 : 0; }
-constexpr int gemm_smem_of(int epi) { return stages_of(epi) * kStageBytes2 + kStagingBytes + extra_staging_of(epi) + 1024 + 256; }
+constexpr int kVecBytes = 2 * BN * 4;                     // bias and column sums of the tile's 256 columns
+constexpr int gemm_smem_of(int epi) { return stages_of(epi) * kStageBytes2 + staging_of(epi) + extra_staging_of(epi) + kVecBytes + 512; }
 
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
@@ -80,16 +84,17 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                   const float* __restrict__ bias, const float* __restrict__ colsum, float* __restrict__ stats,
                   long long M, int N, int K) {
   constexpr int kStages2 = stages_of(EPI);
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem[];                      // SWIZZLE_128B tiles want 1024-byte alignment
+  constexpr int NBUF = fbufs_of(EPI);
   uint8_t* staging = smem + kStages2 * kStageBytes2;
-  uint8_t* staging2 = staging + kStagingBytes;                           // bf16 copy (EPI_RESIDUAL_LN only)
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging2 + extra_staging_of(EPI));
+  uint8_t* staging2 = staging + staging_of(EPI);                         // bf16 copy (EPI_RESIDUAL_LN only)
+  float* vec_s = reinterpret_cast<float*>(staging2 + extra_staging_of(EPI));   // [2][256]: bias, column sums of this tile
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(vec_s) + kVecBytes);
   uint64_t* empty_bar = full_bar + kStages2;
   uint64_t* tmem_full = empty_bar + kStages2;
   uint64_t* tmem_empty = tmem_full + 2;
-  uint64_t* ld_bar = tmem_empty + 2;                                     // [4 warps][2 buffers]: residual tile loads
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(ld_bar + 8);
+  uint64_t* ld_bar = tmem_empty + 2;                                     // [4 warps][4 buffers]: residual tile loads
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(ld_bar + 16);
 
   // warp index and CTA rank are made warp-uniform by construction: the producer and MMA warps then run their loops with
   // uniform control flow and operands (descriptors, coordinates and barrier addresses in uniform registers) and only the
@@ -112,7 +117,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages2; ++i) { ptx::mbar_init(full_bar + i, 1); ptx::mbar_init(empty_bar + i, 1); }
     for (int i = 0; i < 2; ++i) { ptx::mbar_init(tmem_full + i, 1); ptx::mbar_init(tmem_empty + i, 256); }
-    for (int i = 0; i < 8; ++i) ptx::mbar_init(ld_bar + i, 1);
+    for (int i = 0; i < 16; ++i) ptx::mbar_init(ld_bar + i, 1);
     ptx::fence_barrier_init();
   }
   if (warp == 2) {
@@ -174,10 +179,10 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     constexpr bool kF32Out = (EPI == EPI_RESIDUAL_F32 || EPI == EPI_STORE_F32 || EPI == EPI_RESIDUAL_LN);
     constexpr bool kLnIn = (EPI == EPI_LN_BIAS_BF16 || EPI == EPI_LN_QUICKGELU_BF16);
     constexpr int CH = kF32Out ? 32 : 64;
-    uint8_t* my_stage = staging + q * 8192;
+    uint8_t* my_stage = staging + q * (NBUF * 4096);
     uint8_t* my_stage2 = staging2 + q * 8192;
-    uint64_t* my_ld = ld_bar + q * 2;
-    uint32_t ld_phase[2] = {0, 0};
+    uint64_t* my_ld = ld_bar + q * 4;
+    uint32_t ld_phase = 0;                                   // bit b: phase of buffer b's load barrier
     const uint32_t sw = (uint32_t)(lane & 7);
     const uint32_t leader_tmem_empty = ptx::mapa_u32(tmem_empty, 0);
     int acc = 0; uint32_t acc_phase = 0; int buf = 0;
@@ -197,13 +202,26 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
       }
       if (EPI == EPI_RESIDUAL_LN) {
-        // the old residual tile travels into the staging buffer the new one will leave from
+        // the old residual tile travels into the staging buffers the new one will leave from, three chunks ahead
         if (lane == 0) {
           ptx::bulk_wait_group_read<0>();
-          ptx::mbar_arrive_expect_tx(my_ld + buf, 4096);
-          ptx::tma_load_2d(my_stage + buf * 4096, &tmap_out, my_ld + buf, n0, row0);
+#pragma unroll
+          for (int a = 0; a < 3; ++a) {
+            const int b = (buf + a) & 3;
+            ptx::mbar_arrive_expect_tx(my_ld + b, 4096);
+            ptx::tma_load_2d(my_stage + b * 4096, &tmap_out, my_ld + b, n0 + a * CH, row0);
+          }
         }
         __syncwarp();
+      }
+      if (bias != nullptr) {
+        // bias (and column sums) of the tile's 256 columns: once into shared memory -- with the whole L1 carved out for
+        // the operand ring, per-chunk global loads would each pay an L2 round trip
+        asm volatile("bar.sync 1, 128;" ::: "memory");       // the previous tile's readers are done
+        const int e = q * 32 + lane;
+        if (e < 64) reinterpret_cast<float4*>(vec_s)[e] = __ldg(reinterpret_cast<const float4*>(bias + n0) + e);
+        else if (kLnIn) reinterpret_cast<float4*>(vec_s)[e] = __ldg(reinterpret_cast<const float4*>(colsum + n0) + (e - 64));
+        asm volatile("bar.sync 1, 128;" ::: "memory");
       }
       ptx::mbar_wait(tmem_full + acc, acc_phase);
       ptx::tcgen05_fence_after();
@@ -219,39 +237,41 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           ptx::mbar_arrive_cluster(leader_tmem_empty + (uint32_t)(acc * 8));
         }
         if (EPI == EPI_RESIDUAL_LN) {
-          // next chunk's residual tile into the other buffer (its last store has been read out), then wait for this one
+          // the residual tile three chunks ahead goes into the buffer the previous chunk left from (once its store has
+          // been read out); then wait for this chunk's tile
           if (lane == 0) {
             ptx::bulk_wait_group_read<0>();
-            if (c0 + CH < BN) {
-              ptx::mbar_arrive_expect_tx(my_ld + (buf ^ 1), 4096);
-              ptx::tma_load_2d(my_stage + (buf ^ 1) * 4096, &tmap_out, my_ld + (buf ^ 1), n0 + c0 + CH, row0);
+            if (c0 + 3 * CH < BN) {
+              const int b = (buf + 3) & 3;
+              ptx::mbar_arrive_expect_tx(my_ld + b, 4096);
+              ptx::tma_load_2d(my_stage + b * 4096, &tmap_out, my_ld + b, n0 + c0 + 3 * CH, row0);
             }
           }
           __syncwarp();
-          ptx::mbar_wait(my_ld + buf, ld_phase[buf]);
-          ld_phase[buf] ^= 1;
+          ptx::mbar_wait(my_ld + buf, (ld_phase >> buf) & 1u);
+          ld_phase ^= 1u << buf;
         } else {
           if (lane == 0) ptx::bulk_wait_group_read<1>();
           __syncwarp();
         }
         uint8_t* dst = my_stage + buf * 4096 + lane * 128;
         if (kLnIn) {
-          const float4* cp = reinterpret_cast<const float4*>(colsum + n0 + c0);
-          const float4* bp = reinterpret_cast<const float4*>(bias + n0 + c0);
+          const float4* cp = reinterpret_cast<const float4*>(vec_s + BN + c0);
+          const float4* bp = reinterpret_cast<const float4*>(vec_s + c0);
           const float nm = -mean;
 #pragma unroll
           for (int j = 0; j < CH / 4; ++j) {
-            const float4 c = __ldg(cp + j), b = __ldg(bp + j);
+            const float4 c = cp[j], b = bp[j];
             r[4 * j] = __float_as_uint(fmaf(rstd, fmaf(nm, c.x, __uint_as_float(r[4 * j])), b.x));
             r[4 * j + 1] = __float_as_uint(fmaf(rstd, fmaf(nm, c.y, __uint_as_float(r[4 * j + 1])), b.y));
             r[4 * j + 2] = __float_as_uint(fmaf(rstd, fmaf(nm, c.z, __uint_as_float(r[4 * j + 2])), b.z));
             r[4 * j + 3] = __float_as_uint(fmaf(rstd, fmaf(nm, c.w, __uint_as_float(r[4 * j + 3])), b.w));
           }
         } else if (bias != nullptr) {
-          const float4* bp = reinterpret_cast<const float4*>(bias + n0 + c0);
+          const float4* bp = reinterpret_cast<const float4*>(vec_s + c0);
 #pragma unroll
           for (int j = 0; j < CH / 4; ++j) {
-            const float4 b = __ldg(bp + j);
+            const float4 b = bp[j];
             r[4 * j] = __float_as_uint(__uint_as_float(r[4 * j]) + b.x);
             r[4 * j + 1] = __float_as_uint(__uint_as_float(r[4 * j + 1]) + b.y);
             r[4 * j + 2] = __float_as_uint(__uint_as_float(r[4 * j + 2]) + b.z);
@@ -306,7 +326,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             ptx::tma_store_2d(&tmap_out2, my_stage2 + ((c0 >> 6) & 1) * 4096, n0 + c0 - 32, row0);
           ptx::bulk_commit_group();
         }
-        buf ^= 1;
+        buf = (buf + 1) & (NBUF - 1);
       }
       if (EPI == EPI_RESIDUAL_LN) {
         const long long r = (long long)row0 + lane;
