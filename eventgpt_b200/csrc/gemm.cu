@@ -39,7 +39,10 @@ enum { EPI_BIAS_BF16 = 0, EPI_QUICKGELU_BF16 = 1, EPI_GELU_BF16 = 2, EPI_RESIDUA
        //    h (the A operand of the next GEMM) and the per-row sum / sum of squares of this tile's 256 columns;
        // 6, 7: consumer of LayerNorm(h): A is the bf16 copy of h itself, B holds gamma (.) W, and the epilogue applies
        //    rstd * (acc - mean * colsum) + bias' per row (mean, rstd from the four column tiles' partial sums);  7 adds QuickGELU
-       EPI_RESIDUAL_LN = 5, EPI_LN_BIAS_BF16 = 6, EPI_LN_QUICKGELU_BF16 = 7 };
+       EPI_RESIDUAL_LN = 5, EPI_LN_BIAS_BF16 = 6, EPI_LN_QUICKGELU_BF16 = 7,
+       // 5 for a short K (out-proj, K = 1024: the epilogue is the critical path there): four staging tiles per warp so that a
+       // load never waits for the newest store, at the price of an operand stage; chosen by gemm_bf16, not by callers
+       EPI_RESIDUAL_LN_SHORTK = 8 };
 constexpr float kLnEpsG = 1e-5f;
 
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
@@ -68,12 +71,14 @@ __device__ __forceinline__ float activate(float v) {
 constexpr int kBHalfBytes = (BN / 2) * BK * 2;          // 16 KB
 constexpr int kStageBytes2 = kABytes + kBHalfBytes;     // 32 KB per CTA
 // the residual + LayerNorm-statistics epilogue stages a bf16 copy next to the fp32 tile: one operand stage less
-// the residual + LayerNorm-statistics epilogue keeps four fp32 staging tiles per warp in flight (the old residual tile is
-// fetched three chunks ahead) and stages a bf16 copy beside them: two operand stages less
-constexpr int stages_of(int epi) { return epi == EPI_RESIDUAL_LN ? 4 : 6; }
-constexpr int fbufs_of(int epi) { return epi == EPI_RESIDUAL_LN ? 4 : 2; }          // fp32 / bf16 staging tiles (4 KB) per warp
+// the residual + LayerNorm-statistics epilogue keeps three fp32 staging tiles per warp in flight (the old residual tile is
+// fetched two chunks ahead) and stages a bf16 copy beside them: one operand stage less
+constexpr bool is_producer(int epi) { return epi == EPI_RESIDUAL_LN || epi == EPI_RESIDUAL_LN_SHORTK; }
+constexpr int stages_of(int epi) { return epi == EPI_RESIDUAL_LN ? 5 : (epi == EPI_RESIDUAL_LN_SHORTK ? 4 : 6); }
+constexpr int fbufs_of(int epi) { return epi == EPI_RESIDUAL_LN ? 3 : (epi == EPI_RESIDUAL_LN_SHORTK ? 4 : 2); }   // fp32 staging tiles (4 KB) per warp
+constexpr int bbufs_of(int epi) { return epi == EPI_RESIDUAL_LN ? 1 : (epi == EPI_RESIDUAL_LN_SHORTK ? 2 : 0); }   // bf16 staging tiles per warp
 constexpr int staging_of(int epi) { return 4 * fbufs_of(epi) * 4096; }
-constexpr int extra_staging_of(int epi) { return epi == EPI_RESIDUAL_LN ? 4 * 2 * 4096 : 0; }
+constexpr int extra_staging_of(int epi) { return 4 * bbufs_of(epi) * 4096; }
 constexpr int kVecBytes = 2 * BN * 4;                     // bias and column sums of the tile's 256 columns
 constexpr int gemm_smem_of(int epi) { return stages_of(epi) * kStageBytes2 + staging_of(epi) + extra_staging_of(epi) + kVecBytes + 512; }
 
@@ -86,6 +91,8 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   constexpr int kStages2 = stages_of(EPI);
   extern __shared__ __align__(1024) uint8_t smem[];                      // SWIZZLE_128B tiles want 1024-byte alignment
   constexpr int NBUF = fbufs_of(EPI);
+  constexpr bool kProducer = is_producer(EPI);
+  constexpr int kNewest = EPI == EPI_RESIDUAL_LN_SHORTK ? 1 : 0;        // stores that may still be reading when a load is issued
   uint8_t* staging = smem + kStages2 * kStageBytes2;
   uint8_t* staging2 = staging + staging_of(EPI);                         // bf16 copy (EPI_RESIDUAL_LN only)
   float* vec_s = reinterpret_cast<float*>(staging2 + extra_staging_of(EPI));   // [2][256]: bias, column sums of this tile
@@ -112,7 +119,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     ptx::prefetch_tensormap(&tmap_a);
     ptx::prefetch_tensormap(&tmap_b);
     ptx::prefetch_tensormap(&tmap_out);
-    if (EPI == EPI_RESIDUAL_LN) ptx::prefetch_tensormap(&tmap_out2);
+    if (kProducer) ptx::prefetch_tensormap(&tmap_out2);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages2; ++i) { ptx::mbar_init(full_bar + i, 1); ptx::mbar_init(empty_bar + i, 1); }
@@ -176,11 +183,11 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   } else if (warp >= 4) {
     // ===== epilogue (both CTAs, own 128 rows) =====
     const int q = warp & 3;
-    constexpr bool kF32Out = (EPI == EPI_RESIDUAL_F32 || EPI == EPI_STORE_F32 || EPI == EPI_RESIDUAL_LN);
+    constexpr bool kF32Out = (EPI == EPI_RESIDUAL_F32 || EPI == EPI_STORE_F32 || kProducer);
     constexpr bool kLnIn = (EPI == EPI_LN_BIAS_BF16 || EPI == EPI_LN_QUICKGELU_BF16);
     constexpr int CH = kF32Out ? 32 : 64;
     uint8_t* my_stage = staging + q * (NBUF * 4096);
-    uint8_t* my_stage2 = staging2 + q * 8192;
+    uint8_t* my_stage2 = staging2 + q * (bbufs_of(EPI) * 4096);
     uint64_t* my_ld = ld_bar + q * 4;
     uint32_t ld_phase = 0;                                   // bit b: phase of buffer b's load barrier
     const uint32_t sw = (uint32_t)(lane & 7);
@@ -201,13 +208,13 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           rstd = rsqrtf(fmaxf(var, 0.f) + kLnEpsG);
         }
       }
-      if (EPI == EPI_RESIDUAL_LN) {
-        // the old residual tile travels into the staging buffers the new one will leave from, three chunks ahead
+      if (kProducer) {
+        // the old residual tile travels into the staging buffers the new one will leave from, two chunks ahead
         if (lane == 0) {
-          ptx::bulk_wait_group_read<0>();
+          ptx::bulk_wait_group_read<kNewest>();
 #pragma unroll
-          for (int a = 0; a < 3; ++a) {
-            const int b = (buf + a) & 3;
+          for (int a = 0; a < 2; ++a) {
+            const int b = (buf + a) % NBUF;
             ptx::mbar_arrive_expect_tx(my_ld + b, 4096);
             ptx::tma_load_2d(my_stage + b * 4096, &tmap_out, my_ld + b, n0 + a * CH, row0);
           }
@@ -236,15 +243,16 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           ptx::tcgen05_fence_before();
           ptx::mbar_arrive_cluster(leader_tmem_empty + (uint32_t)(acc * 8));
         }
-        if (EPI == EPI_RESIDUAL_LN) {
-          // the residual tile three chunks ahead goes into the buffer the previous chunk left from (once its store has
-          // been read out); then wait for this chunk's tile
+        if (kProducer) {
+          // the residual tile two chunks ahead goes into a buffer whose store has been read out (ring of three: the previous
+          // chunk's, so the newest store is waited for; ring of four: the one before, and the newest store stays in flight);
+          // the same wait frees the bf16 tile about to be rewritten.  Then wait for this chunk's tile
           if (lane == 0) {
-            ptx::bulk_wait_group_read<0>();
-            if (c0 + 3 * CH < BN) {
-              const int b = (buf + 3) & 3;
+            ptx::bulk_wait_group_read<kNewest>();
+            if (c0 + 2 * CH < BN) {
+              const int b = (buf + 2) % NBUF;
               ptx::mbar_arrive_expect_tx(my_ld + b, 4096);
-              ptx::tma_load_2d(my_stage + b * 4096, &tmap_out, my_ld + b, n0 + c0 + 3 * CH, row0);
+              ptx::tma_load_2d(my_stage + b * 4096, &tmap_out, my_ld + b, n0 + c0 + 2 * CH, row0);
             }
           }
           __syncwarp();
@@ -258,14 +266,15 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         if (kLnIn) {
           const float4* cp = reinterpret_cast<const float4*>(vec_s + BN + c0);
           const float4* bp = reinterpret_cast<const float4*>(vec_s + c0);
-          const float nm = -mean;
+          // rstd * acc + (bias' - rstd * mean * colsum)
+          const float nmr = -mean * rstd;
 #pragma unroll
           for (int j = 0; j < CH / 4; ++j) {
             const float4 c = cp[j], b = bp[j];
-            r[4 * j] = __float_as_uint(fmaf(rstd, fmaf(nm, c.x, __uint_as_float(r[4 * j])), b.x));
-            r[4 * j + 1] = __float_as_uint(fmaf(rstd, fmaf(nm, c.y, __uint_as_float(r[4 * j + 1])), b.y));
-            r[4 * j + 2] = __float_as_uint(fmaf(rstd, fmaf(nm, c.z, __uint_as_float(r[4 * j + 2])), b.z));
-            r[4 * j + 3] = __float_as_uint(fmaf(rstd, fmaf(nm, c.w, __uint_as_float(r[4 * j + 3])), b.w));
+            r[4 * j] = __float_as_uint(fmaf(rstd, __uint_as_float(r[4 * j]), fmaf(nmr, c.x, b.x)));
+            r[4 * j + 1] = __float_as_uint(fmaf(rstd, __uint_as_float(r[4 * j + 1]), fmaf(nmr, c.y, b.y)));
+            r[4 * j + 2] = __float_as_uint(fmaf(rstd, __uint_as_float(r[4 * j + 2]), fmaf(nmr, c.z, b.z)));
+            r[4 * j + 3] = __float_as_uint(fmaf(rstd, __uint_as_float(r[4 * j + 3]), fmaf(nmr, c.w, b.w)));
           }
         } else if (bias != nullptr) {
           const float4* bp = reinterpret_cast<const float4*>(vec_s + c0);
@@ -278,9 +287,9 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             r[4 * j + 3] = __float_as_uint(__uint_as_float(r[4 * j + 3]) + b.w);
           }
         }
-        if (EPI == EPI_RESIDUAL_LN) {
+        if (kProducer) {
           // h_new = h_old + acc + bias in place in the staging tile; bf16 copy beside it; running row statistics
-          uint8_t* dst2 = my_stage2 + ((c0 >> 6) & 1) * 4096 + lane * 128;
+          uint8_t* dst2 = my_stage2 + (bbufs_of(EPI) == 2 ? ((c0 >> 6) & 1) * 4096 : 0) + lane * 128;
           const uint32_t half = (uint32_t)((c0 >> 5) & 1) * 4u;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -322,13 +331,13 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         if (lane == 0) {
           if (EPI == EPI_RESIDUAL_F32) ptx::tma_reduce_add_2d(&tmap_out, my_stage + buf * 4096, n0 + c0, row0);
           else ptx::tma_store_2d(&tmap_out, my_stage + buf * 4096, n0 + c0, row0);
-          if (EPI == EPI_RESIDUAL_LN && (c0 & 32))           // two 32-column chunks make one 64-column bf16 tile
-            ptx::tma_store_2d(&tmap_out2, my_stage2 + ((c0 >> 6) & 1) * 4096, n0 + c0 - 32, row0);
+          if (kProducer && (c0 & 32))                        // two 32-column chunks make one 64-column bf16 tile
+            ptx::tma_store_2d(&tmap_out2, my_stage2 + (bbufs_of(EPI) == 2 ? ((c0 >> 6) & 1) * 4096 : 0), n0 + c0 - 32, row0);
           ptx::bulk_commit_group();
         }
-        buf = (buf + 1) & (NBUF - 1);
+        buf = buf + 1 == NBUF ? 0 : buf + 1;
       }
-      if (EPI == EPI_RESIDUAL_LN) {
+      if (kProducer) {
         const long long r = (long long)row0 + lane;
         if (r < M) *reinterpret_cast<float2*>(stats + r * 8 + 2 * (n0 / BN)) = make_float2(s1, s2);
       }
@@ -418,7 +427,9 @@ int gemm_bf16(const void* A, const void* B, const float* bias, void* out, long l
     case EPI_GELU_BF16: return launch_gemm2<EPI_GELU_BF16>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
     case EPI_RESIDUAL_F32: return launch_gemm2<EPI_RESIDUAL_F32>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
     case EPI_STORE_F32: return launch_gemm2<EPI_STORE_F32>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
-    case EPI_RESIDUAL_LN: return launch_gemm2<EPI_RESIDUAL_LN>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
+    case EPI_RESIDUAL_LN:
+      if (K <= 2048) return launch_gemm2<EPI_RESIDUAL_LN_SHORTK>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
+      return launch_gemm2<EPI_RESIDUAL_LN>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
     case EPI_LN_BIAS_BF16: return launch_gemm2<EPI_LN_BIAS_BF16>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
     case EPI_LN_QUICKGELU_BF16: return launch_gemm2<EPI_LN_QUICKGELU_BF16>(ta, tb, to, to2, bias, colsum, stats, M, N, K, stream);
   }
