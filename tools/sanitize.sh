@@ -2,10 +2,14 @@
 # compute-sanitizer over the integer kernels and a 2-layer token call: memcheck, racecheck, synccheck.
 # Usage (GPU box): bash tools/sanitize.sh > gpurun_out/sanitizer.log 2>&1
 set -u
+CS=$(command -v compute-sanitizer || echo /usr/local/cuda/bin/compute-sanitizer)
+$CS --version | head -2
 run() {   # tool, label, command...
   tool=$1; label=$2; shift 2
   echo "=== compute-sanitizer --tool $tool : $label"
-  timeout 900 compute-sanitizer --tool "$tool" --print-limit 5 "$@" 2>&1 | grep -E "ERROR SUMMARY|RACECHECK SUMMARY|Error:|hazard|passed|failed" | tail -6
+  timeout 900 $CS --tool "$tool" --print-limit 5 "$@" > /tmp/cs.log 2>&1
+  echo "exit code $?"
+  grep -E "ERROR SUMMARY|RACECHECK SUMMARY|Error:|hazard|passed|failed|error" /tmp/cs.log | tail -6
 }
 RASTER='tests/test_gpu_events.py -x -q -m gpu -k "bit_exact and (sample1 or adv_zipf or adv_n5 or synthetic_000003) or batched_ragged or generic_dtypes or device_clip or split"'
 for tool in memcheck racecheck synccheck; do
