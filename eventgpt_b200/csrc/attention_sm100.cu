@@ -51,10 +51,6 @@ constexpr int kSmemXch = kSmemBar + 512;                  // float [3 (max, sum,
 constexpr int kSmemStage = kSmemXch + 6 * 1024;           // output staging: 8 warps x (32 rows x 64 B)
 constexpr int kStageBytes = 32 * 64;
 constexpr int kSmemTotal = kSmemStage + 8 * kStageBytes + 1024;   // + alignment slack
-#ifndef EGPT_ATTN_STAGGER
-#define EGPT_ATTN_STAGGER 900
-#endif
-constexpr int kStagger = EGPT_ATTN_STAGGER;               // cycles by which key group 1 starts behind group 0
 constexpr int kTmemCols = 512;
 constexpr uint32_t kTmemS = 0, kTmemO = 4 * kBlk;         // columns: S/P [group][buffer][96], then O [group][64]
 #ifndef EGPT_ATTN_POLY_EVERY
@@ -160,6 +156,7 @@ struct Bars {
   uint64_t o_free;                       // the tile's two partial outputs were read out by all 256 threads
   uint64_t t_done;                       // per tile: both groups' (max, sum, dot) are in shared memory (256 arrivals) and
                                          // both groups' last P V has retired (2 commits)
+  uint64_t stagger;                      // per head: key group 0 is two thirds through the exp2 of its first block (4 warps)
   uint32_t tmem_ptr;
 };
 
@@ -217,6 +214,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     }
     ptx::mbar_init(&bars->o_free, 256);
     ptx::mbar_init(&bars->t_done, 258);
+    ptx::mbar_init(&bars->stagger, 4);
     ptx::fence_barrier_init();
   }
   if (warp == 10) {
@@ -435,9 +433,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           if (gi == 1 && t == tb && j == 0) {
             // Run the two key groups out of phase: while one is in its exp2 stretch (MUFU bound) the other loads, reduces,
             // merges or waits.  Both groups meet at a head's first S block (they wait for the same K / Q loads), so the
-            // offset is re-established there; in between they only share mbarriers that are long complete when polled.
-            const long long t0 = clock64();
-            while (clock64() - t0 < kStagger) { }
+            // offset is re-established there: group 1 starts this block only when group 0 is two thirds through the exp2
+            // of its own first block (an event, not a count of clock cycles).  Group 0 cannot be a head ahead here: every
+            // tile's merge needs both groups, so the parity wait is exact.
+            ptx::mbar_wait(&bars->stagger, (uint32_t)(it & 1));
           }
           ptx::tcgen05_fence_after();
           if (trc) TR(warp * 256 + n * 16 + 1);
@@ -519,6 +518,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
               wd[i] = pack2(pp.x, pp.y);
             }
             tmem_st_32x32b_x16(ts + (uint32_t)(16 * c), wd);          // P over S: column c <- keys 2c, 2c+1
+            if (gi == 0 && c == 1 && t == tb && j == 0) {              // lets group 1 start its first block of this head
+              __syncwarp();
+              if (lane == 0) ptx::mbar_arrive(&bars->stagger);
+            }
           }
           l += (s2[0].x + s2[0].y) + (s2[1].x + s2[1].y);
           if (trc) TR(warp * 256 + n * 16 + 4);
