@@ -31,7 +31,6 @@ namespace egpt {
 constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16;
 constexpr int kABytes = BM * BK * 2;               // 16 KB
 constexpr int kTmemCols = 2 * BN;                  // two accumulator stages
-constexpr int kGemmThreads = 256;
 
 enum { EPI_BIAS_BF16 = 0, EPI_QUICKGELU_BF16 = 1, EPI_GELU_BF16 = 2, EPI_RESIDUAL_F32 = 3, EPI_STORE_F32 = 4,
        // LayerNorm folded into the two GEMMs around it (the separate LayerNorm pass over the residual stream disappears):
@@ -73,17 +72,27 @@ constexpr int kStageBytes2 = kABytes + kBHalfBytes;     // 32 KB per CTA
 // the residual + LayerNorm-statistics epilogue stages a bf16 copy next to the fp32 tile: one operand stage less
 // the residual + LayerNorm-statistics epilogue keeps three fp32 staging tiles per warp in flight (the old residual tile is
 // fetched two chunks ahead) and stages a bf16 copy beside them: one operand stage less
+// The bf16-output epilogues (bias, activations, folded LayerNorm) run on EIGHT warps: two per TMEM lane quarter, each taking
+// half of the tile's 256 columns.  One warp per scheduler left fc1's QuickGELU + LayerNorm epilogue latency-bound (tensor
+// pipe 82 % active); the fp32-output epilogues are bound by memory or by the MMA and keep four warps.
+constexpr int epi_warps_of(int epi) {
+  return (epi == EPI_BIAS_BF16 || epi == EPI_QUICKGELU_BF16 || epi == EPI_GELU_BF16 || epi == EPI_LN_BIAS_BF16 ||
+          epi == EPI_LN_QUICKGELU_BF16) ? 8 : 4;
+}
+constexpr int threads_of(int epi) { return 128 + 32 * epi_warps_of(epi); }
 constexpr bool is_producer(int epi) { return epi == EPI_RESIDUAL_LN || epi == EPI_RESIDUAL_LN_SHORTK; }
 constexpr int stages_of(int epi) { return epi == EPI_RESIDUAL_LN ? 5 : (epi == EPI_RESIDUAL_LN_SHORTK ? 4 : 6); }
-constexpr int fbufs_of(int epi) { return epi == EPI_RESIDUAL_LN ? 3 : (epi == EPI_RESIDUAL_LN_SHORTK ? 4 : 2); }   // fp32 staging tiles (4 KB) per warp
+constexpr int fbufs_of(int epi) {            // staging tiles (4 KB) per epilogue warp
+  return epi == EPI_RESIDUAL_LN ? 3 : (epi == EPI_RESIDUAL_LN_SHORTK ? 4 : (epi_warps_of(epi) == 8 ? 1 : 2));
+}
 constexpr int bbufs_of(int epi) { return epi == EPI_RESIDUAL_LN ? 1 : (epi == EPI_RESIDUAL_LN_SHORTK ? 2 : 0); }   // bf16 staging tiles per warp
-constexpr int staging_of(int epi) { return 4 * fbufs_of(epi) * 4096; }
+constexpr int staging_of(int epi) { return epi_warps_of(epi) * fbufs_of(epi) * 4096; }
 constexpr int extra_staging_of(int epi) { return 4 * bbufs_of(epi) * 4096; }
 constexpr int kVecBytes = 2 * BN * 4;                     // bias and column sums of the tile's 256 columns
 constexpr int gemm_smem_of(int epi) { return stages_of(epi) * kStageBytes2 + staging_of(epi) + extra_staging_of(epi) + kVecBytes + 512; }
 
 template <int EPI>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_of(EPI), 1)
 gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_out2,
                   const float* __restrict__ bias, const float* __restrict__ colsum, float* __restrict__ stats,
@@ -123,7 +132,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages2; ++i) { ptx::mbar_init(full_bar + i, 1); ptx::mbar_init(empty_bar + i, 1); }
-    for (int i = 0; i < 2; ++i) { ptx::mbar_init(tmem_full + i, 1); ptx::mbar_init(tmem_empty + i, 256); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(tmem_full + i, 1); ptx::mbar_init(tmem_empty + i, 2 * 32 * epi_warps_of(EPI)); }
     for (int i = 0; i < 16; ++i) ptx::mbar_init(ld_bar + i, 1);
     ptx::fence_barrier_init();
   }
@@ -182,11 +191,15 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     }
   } else if (warp >= 4) {
     // ===== epilogue (both CTAs, own 128 rows) =====
-    const int q = warp & 3;
+    constexpr int kEpiWarps = epi_warps_of(EPI);
+    constexpr int kSpan = BN / (kEpiWarps / 4);                 // columns of the tile this warp drains
+    const int q = warp & 3;                                     // TMEM lane quarter (rows q*32 .. q*32+31 of the CTA's 128)
+    const int ew = warp - 4;                                    // epilogue warp 0 .. kEpiWarps-1
+    const int col_lo = (ew >> 2) * kSpan;
     constexpr bool kF32Out = (EPI == EPI_RESIDUAL_F32 || EPI == EPI_STORE_F32 || kProducer);
     constexpr bool kLnIn = (EPI == EPI_LN_BIAS_BF16 || EPI == EPI_LN_QUICKGELU_BF16);
     constexpr int CH = kF32Out ? 32 : 64;
-    uint8_t* my_stage = staging + q * (NBUF * 4096);
+    uint8_t* my_stage = staging + ew * (NBUF * 4096);
     uint8_t* my_stage2 = staging2 + q * (bbufs_of(EPI) * 4096);
     uint64_t* my_ld = ld_bar + q * 4;
     uint32_t ld_phase = 0;                                   // bit b: phase of buffer b's load barrier
@@ -224,22 +237,22 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       if (bias != nullptr) {
         // bias (and column sums) of the tile's 256 columns: once into shared memory -- with the whole L1 carved out for
         // the operand ring, per-chunk global loads would each pay an L2 round trip
-        asm volatile("bar.sync 1, 128;" ::: "memory");       // the previous tile's readers are done
-        const int e = q * 32 + lane;
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");       // the previous tile's readers are done
+        const int e = ew * 32 + lane;
         if (e < 64) reinterpret_cast<float4*>(vec_s)[e] = __ldg(reinterpret_cast<const float4*>(bias + n0) + e);
-        else if (kLnIn) reinterpret_cast<float4*>(vec_s)[e] = __ldg(reinterpret_cast<const float4*>(colsum + n0) + (e - 64));
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        else if (kLnIn && e < 128) reinterpret_cast<float4*>(vec_s)[e] = __ldg(reinterpret_cast<const float4*>(colsum + n0) + (e - 64));
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
       }
       ptx::mbar_wait(tmem_full + acc, acc_phase);
       ptx::tcgen05_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += CH) {
+      for (int c0 = col_lo; c0 < col_lo + kSpan; c0 += CH) {
         uint32_t r[CH];
         ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
         if (CH == 64) ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0 + 32u, *reinterpret_cast<uint32_t(*)[32]>(&r[CH - 32]));
         ptx::tmem_ld_wait();
-        if (c0 + CH == BN) {
+        if (c0 + CH == col_lo + kSpan) {
           ptx::tcgen05_fence_before();
           ptx::mbar_arrive_cluster(leader_tmem_empty + (uint32_t)(acc * 8));
         }
@@ -259,7 +272,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           ptx::mbar_wait(my_ld + buf, (ld_phase >> buf) & 1u);
           ld_phase ^= 1u << buf;
         } else {
-          if (lane == 0) ptx::bulk_wait_group_read<1>();
+          if (lane == 0) ptx::bulk_wait_group_read<NBUF - 1>();      // the store that last read this staging tile is done with it
           __syncwarp();
         }
         uint8_t* dst = my_stage + buf * 4096 + lane * 128;
@@ -395,7 +408,7 @@ static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUte
   EGPT_CUDA(cudaFuncSetAttribute(gemm2_bf16_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const long long pairs = ((M + 2 * BM - 1) / (2 * BM)) * (N / BN);
   const int grid = (int)(2 * (pairs < kNumSMs / 2 ? pairs : kNumSMs / 2));
-  gemm2_bf16_kernel<EPI><<<grid, kGemmThreads, smem, stream>>>(ta, tb, to, to2, bias, colsum, stats, M, N, K);
+  gemm2_bf16_kernel<EPI><<<grid, threads_of(EPI), smem, stream>>>(ta, tb, to, to2, bias, colsum, stats, M, N, K);
   EGPT_LAUNCH_CHECK();
   return EGPT_OK;
 }
