@@ -6,7 +6,7 @@
 // :84-85,338).  nn.Linear stores weight as [out, in] = [N, K] K-major, which is
 // exactly the B operand layout tcgen05 wants, so weights are used as they are.
 //
-// Structure: persistent, one CTA per SM, CTAs paired in clusters of 2 (tcgen05 cta_group::2), 256 threads:
+// Structure: persistent, one CTA per SM, CTAs paired in clusters of 2 (tcgen05 cta_group::2), 256 or 384 threads:
 //   warp 0    TMA producer (both CTAs): own 128 x 64 slice of A and HALF (128 rows) of the 256 x 64 B tile,
 //             SWIZZLE_128B, 6-stage mbarrier ring (32 KB per stage per SM); completion bytes of both CTAs
 //             are credited to the leader CTA's "full" barrier
@@ -14,10 +14,11 @@
 //             fp32 accumulators in both CTAs' TMEM, double-buffered (2 x 256 columns); commits are
 //             multicast to both CTAs ("slot free", "accumulator ready")
 //   warp 2    TMEM allocator
-//   warps 4-7 epilogue (both CTAs, own 128 rows): tcgen05.ld 32 lanes x 32 columns -> bias / activation ->
-//             128-byte swizzled staging rows in shared memory -> TMA store (bf16 / fp32), or TMA reduce-add
-//             for the fp32 residual stream (h += acc + bias is done in L2; the SM never reads h).  Rows past
-//             M are clipped by the TMA unit.
+//   warps 4.. epilogue (both CTAs, own 128 rows): tcgen05.ld 32 lanes x 32 columns -> bias / activation / folded
+//             LayerNorm -> 128-byte swizzled staging rows in shared memory -> TMA store.  Eight warps (two per TMEM
+//             lane quarter, half the tile's columns each) for the bf16-output epilogues, four for the fp32-output ones:
+//             plain store, TMA reduce-add (h += acc + bias done in L2), or the residual read-add-store that also emits
+//             the bf16 copy and the LayerNorm partial sums (see the epilogue enum).  Rows past M are clipped by the TMA unit.
 // Tiles are walked n-fastest so the CTA pairs running concurrently share A rows through L2.
 // Measured (profiles/r01_bench_history.md): a single-CTA 128x256 version with 4 x 48 KB stages spent 17-33 % of
 // the MMA thread's time waiting for operand data; pairing CTAs cut the L2 -> SM operand traffic by a third and

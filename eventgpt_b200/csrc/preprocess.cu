@@ -270,6 +270,9 @@ extern "C" int egpt_preprocess(const uint8_t* frames, size_t frame_stride, const
   EGPT_CHECK_ARG(frames && hw && status && workspace, "egpt_preprocess: null pointer argument");
   EGPT_CHECK_ARG(out_pixel_values || out_patches, "egpt_preprocess: no output requested");
   EGPT_CHECK_ARG(n_frames_total > 0 && max_h > 0, "egpt_preprocess: n_frames_total=%d max_h=%d", n_frames_total, max_h);
+  EGPT_CHECK_ARG(((uintptr_t)frames & 15) == 0 && frame_stride % 16 == 0 && ((uintptr_t)workspace & 15) == 0 &&
+                 ((uintptr_t)out_pixel_values & 15) == 0 && ((uintptr_t)out_patches & 15) == 0,
+                 "egpt_preprocess: frames, frame_stride, outputs and workspace must be 16-byte aligned");
   if (workspace_bytes < egpt_preprocess_workspace_bytes(n_frames_total, max_h)) {
     set_error("egpt_preprocess: workspace %zu < %zu bytes", workspace_bytes,
               egpt_preprocess_workspace_bytes(n_frames_total, max_h));

@@ -16,7 +16,7 @@ for r in rows[1:]:
     tot[name] += us
     cnt[name] += 1
 T = sum(tot.values())
-print("# Round 1 — ncu launch list of `python bench.py --steps 2 --warmup 3 --no-cpu-baseline` (first 1300 launches)\n")
+print("# ncu launch list of `python bench.py --steps 2 --warmup 3 --no-cpu-baseline` (first 1300 launches)\n")
 print("`ncu --metrics gpu__time_duration.sum --clock-control none -c 1300` after the same command exited 0 without ncu (same gpurun call).")
 print(f"Serialised, cold-cache: compare SHARES.  State of the code: {state}\n")
 print("| kernel | launches | total us | share |\n|---|---:|---:|---:|")
