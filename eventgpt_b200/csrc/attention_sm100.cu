@@ -3,7 +3,7 @@
 // called from model/EventChatModel.py:196).  Input: packed QKV projection [F*577, 3072] bf16
 // (q pre-scaled by 1/8 in the weights); output bf16 [F*577, 1024].
 //
-// Persistent CTAs of 384 threads, one per SM, each working through a contiguous range of (frame, head, Q tile)
+// Persistent CTAs of 512 threads, one per SM, each working through a contiguous range of (frame, head, Q tile)
 // units.  The 577 keys of a head are split into two key groups of 288 (three blocks of 96) plus one left-over
 // key; each group is an independent flash-attention pipeline over the same 128-row Q tile, and the two partial
 // results of a row are merged once per tile:
@@ -11,19 +11,22 @@
 //              registers, P_n = exp2(S_n - m) goes back over it as packed bf16 (tcgen05.st), the group's partial
 //              output accumulates in TMEM across the three blocks and is rescaled in place only when a block
 //              raises the row maximum by more than 2^8 (otherwise the stale maximum is kept: p <= 256 is harmless
-//              in fp32 / bf16).  A quarter of the exp2 runs as a cubic on the FMA pipe.  The merge of tile t
-//              (two partial outputs + the left-over key, which is handled on the CUDA cores: a 64-long dot
-//              product per row) is deferred until the first block of tile t+1 has been handed to the tensor
-//              pipe, so no softmax warp ever waits for a P V product to retire.
-//   warp 8     TMA producer: K and V of a head (576 rows x 64 in blocks of 96, each block re-loaded for the next
+//              in fp32 / bf16).  A quarter of the exp2 runs as a cubic on the FMA pipe.  The softmax warps do
+//              nothing else: at the end of a tile they publish (max, sum) and go straight on to the next tile.
+//   warps 8-11 merge / output: one thread per row.  The left-over key 576 is handled here on the CUDA cores (a
+//              64-long dot product per row, computed one tile ahead while the Q tile is still resident); when both
+//              groups' last P V of tile t has retired the thread reads the two partial outputs from TMEM, combines
+//              them with the left-over key's term and normalises, and the warp stores its 32 rows x 64 dims with one
+//              TMA store.  This used to run inside the softmax warps and cost them a third of every tile.
+//   warp 12    TMA producer: K and V of a head (576 rows x 64 in blocks of 96, each block re-loaded for the next
 //              head as soon as the current head's last product on it has retired; rows 576..591 -- key 576 and
 //              zero fill from the 3-D tensor map -- in a small double buffer), 128-row Q tiles into a double buffer
-//   warps 9/11 MMA issuer of group 0 / 1 (one thread each): S_n = Q K_n^T (M128 x N96 x K64, SS) into a double
+//   warps 13/15 MMA issuer of group 0 / 1 (one thread each): S_n = Q K_n^T (M128 x N96 x K64, SS) into a double
 //              buffer, O_g += P_n V_n (TS form: P read from TMEM, V from shared memory as an MN-major operand)
-//   warp 10    TMEM allocator (2 groups x 2 x 96 columns for S / P, 2 x 64 for the partial outputs)
+//   warp 14    TMEM allocator (2 groups x 2 x 96 columns for S / P, 2 x 64 for the partial outputs)
 // The control warps sit in the highest warp ids: the warp arbiter favours them, and the single-thread issuers
-// must not starve for issue slots behind eight busy softmax warps.  Registers are handed from the control
-// warps to the softmax warps with setmaxnreg.
+// must not starve for issue slots behind the busy softmax warps.  Registers are handed from the control and merge
+// warps to the softmax warps with setmaxnreg (56 / 72 / 192 per thread).
 #include "common.cuh"
 #include "sm100_ptx.cuh"
 
@@ -39,18 +42,19 @@ constexpr int kBlk = 96;                                  // keys per block
 constexpr int kGroupKeys = 3 * kBlk;                      // 288: key group 0 = keys [0,288), group 1 = [288,576)
 constexpr int kXKey = 2 * kGroupKeys;                     // 576: the left-over key, handled outside the MMAs
 constexpr int kNBlk = 3;                                  // blocks per group and tile
-constexpr int kThreads = 384;
+constexpr int kThreads = 512;
 constexpr int kRowBytes = 128;                            // 64 bf16
 constexpr int kKVBytes = kXKey * kRowBytes;               // 73728: 576 keys
 constexpr int kQBytes = kQTile * kRowBytes;               // 16384
 constexpr int kXBytes = 16 * kRowBytes;                   // rows 576..591 of K or V (key 576 + zero fill)
 constexpr int kSmemK = 0, kSmemV = kKVBytes, kSmemQ = 2 * kKVBytes;
 constexpr int kSmemX = kSmemQ + 2 * kQBytes;              // [2 (head parity)][2 (K, V)][16 rows]
-constexpr int kSmemBar = kSmemX + 4 * kXBytes;
-constexpr int kSmemXch = kSmemBar + 512;                  // float [3 (max, sum, partial dot)][2 (tile parity)][2 (group)][128]
-constexpr int kSmemStage = kSmemXch + 6 * 1024;           // output staging: 8 warps x (32 rows x 64 B)
-constexpr int kStageBytes = 32 * 64;
-constexpr int kSmemTotal = kSmemStage + 8 * kStageBytes + 1024;   // + alignment slack
+constexpr int kSmemStage = kSmemX + 4 * kXBytes;          // output staging: 4 merge warps x (32 rows x 128 B), SWIZZLE_128B,
+constexpr int kStageBytes = 32 * kRowBytes;               // so each slab sits on a 1024-byte boundary
+static_assert(kSmemStage % 1024 == 0, "swizzled staging slabs must be 1024-byte aligned");
+constexpr int kSmemBar = kSmemStage + 4 * kStageBytes;
+constexpr int kSmemXch = kSmemBar + 512;                  // float [2 (max, sum)][2 (tile parity)][2 (group)][128]
+constexpr int kSmemTotal = kSmemXch + 4 * 1024 + 1024;    // + alignment slack
 constexpr int kTmemCols = 512;
 constexpr uint32_t kTmemS = 0, kTmemO = 4 * kBlk;         // columns: S/P [group][buffer][96], then O [group][64]
 #ifndef EGPT_ATTN_POLY_EVERY
@@ -148,13 +152,13 @@ __device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, u
 struct Bars {
   uint64_t k_full[2][kNBlk], v_full[2][kNBlk];   // per head: a 96-key block of K / V landed
   uint64_t k_free[2][kNBlk], v_free[2][kNBlk];   // per head: the head's last product on that block retired (commit)
-  uint64_t x_full[2], x_free[2];         // [head parity]: rows 576..591 of K and V landed / were last read (256 arrivals)
+  uint64_t x_full[2], x_free[2];         // [head parity]: rows 576..591 of K and V landed / were last read (128 arrivals)
   uint64_t q_full[2], q_empty[2];        // Q tile double buffer; q_empty counts both issuers
   uint64_t s_full[2][2];                 // [group][buffer]: S block landed
   uint64_t p_full[2][2];                 // [group][buffer]: P stored over it by the group's 128 threads
   uint64_t o_done[2][2];                 // [group][block parity]: P V of a block retired
-  uint64_t o_free;                       // the tile's two partial outputs were read out by all 256 threads
-  uint64_t t_done;                       // per tile: both groups' (max, sum, dot) are in shared memory (256 arrivals) and
+  uint64_t o_free;                       // the tile's two partial outputs were read out by the 128 merge threads
+  uint64_t t_done;                       // per tile: both groups' (max, sum) are in shared memory (256 arrivals) and
                                          // both groups' last P V has retired (2 commits)
   uint64_t stagger;                      // per head: key group 0 is two thirds through the exp2 of its first block (4 warps)
   uint32_t tmem_ptr;
@@ -199,25 +203,25 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   auto tile_begin = [&](int it) { return it == 0 ? g0 - head0 * kQTiles : 0; };
   auto tile_end = [&](int it) { return it == n_it - 1 ? g1 - (head0 + it) * kQTiles : kQTiles; };
 
-  if (warp == 8 && lane == 0) { ptx::prefetch_tensormap(&tmap_q); ptx::prefetch_tensormap(&tmap_kv); ptx::prefetch_tensormap(&tmap_out); }
-  if (warp == 9 && lane == 0) {
+  if (warp == 12 && lane == 0) { ptx::prefetch_tensormap(&tmap_q); ptx::prefetch_tensormap(&tmap_kv); ptx::prefetch_tensormap(&tmap_out); }
+  if (warp == 13 && lane == 0) {
     for (int g = 0; g < 2; ++g) {
       for (int i = 0; i < kNBlk; ++i) {
         ptx::mbar_init(&bars->k_full[g][i], 1); ptx::mbar_init(&bars->v_full[g][i], 1);
         ptx::mbar_init(&bars->k_free[g][i], 1); ptx::mbar_init(&bars->v_free[g][i], 1);
       }
-      ptx::mbar_init(&bars->x_full[g], 1); ptx::mbar_init(&bars->x_free[g], 256);
+      ptx::mbar_init(&bars->x_full[g], 1); ptx::mbar_init(&bars->x_free[g], 128);
       ptx::mbar_init(&bars->q_full[g], 1); ptx::mbar_init(&bars->q_empty[g], 2);
       for (int i = 0; i < 2; ++i) {
         ptx::mbar_init(&bars->s_full[g][i], 1); ptx::mbar_init(&bars->p_full[g][i], 128); ptx::mbar_init(&bars->o_done[g][i], 1);
       }
     }
-    ptx::mbar_init(&bars->o_free, 256);
+    ptx::mbar_init(&bars->o_free, 128);
     ptx::mbar_init(&bars->t_done, 258);
     ptx::mbar_init(&bars->stagger, 4);
     ptx::fence_barrier_init();
   }
-  if (warp == 10) {
+  if (warp == 14) {
     ptx::tmem_alloc(&bars->tmem_ptr, kTmemCols);
     ptx::tmem_relinquish();
   }
@@ -226,9 +230,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   ptx::tcgen05_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, bars->tmem_ptr, 0);
 
-  if (warp >= 8) {
+  if (warp >= 12) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
-    if (warp == 8 && lane == 0) {
+    if (warp == 12 && lane == 0) {
       // ===== TMA producer =====
       int T = 0;                                                       // tiles loaded so far
       for (int it = 0; it < n_it; ++it) {
@@ -270,10 +274,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         }
         for (int t = tb + 2; t < te; ++t) load_q(t);
       }
-    } else if (warp == 9 || warp == 11) {
+    } else if (warp == 13 || warp == 15) {
       // ===== MMA issuer of key group gi: an independent in-order stream of S and P V products.  The whole warp walks the
       // loop (uniform control flow and operands, so descriptors live in uniform registers); one elected lane issues =====
-      const int gi = warp == 9 ? 0 : 1;
+      const int gi = warp == 13 ? 0 : 1;
       const uint64_t dK0 = ptx::make_smem_desc_sw128(ptx::smem_u32(smem + kSmemK + gi * kGroupKeys * kRowBytes));
       const uint64_t dV0 = make_desc_mn_sw128(ptx::smem_u32(smem + kSmemV + gi * kGroupKeys * kRowBytes));
       const uint64_t dQ0 = ptx::make_smem_desc_sw128(ptx::smem_u32(smem + kSmemQ));
@@ -337,8 +341,98 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       }
       issue_pv(N - 1, p_it, p_T, p_j, p_first, p_last);
     }
+  } else if (warp >= 8) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+    // ===== merge / output: thread = row r of the tile, all 64 dims.  Runs one tile behind the softmax warps. =====
+    const int q = warp & 3;
+    const int r = q * 32 + lane;                       // row inside the tile == TMEM lane
+    const uint32_t lane_base = (uint32_t)(q * 32) << 16;
+    const uint32_t tmem_oa = tmem_base + lane_base + kTmemO, tmem_ob = tmem_oa + (uint32_t)kD;
+    const float* xch = reinterpret_cast<const float*>(smem + kSmemXch);     // [2][2 (tile parity)][2 (group)][128]
+    uint8_t* stage = smem + kSmemStage + q * kStageBytes;
+    constexpr float kLog2e = 1.4426950408889634f;
+    // q_r . k_576 of local tile T (head it of this CTA): the Q tile and the head's rows 576.. are TMA-written, the waits are
+    // the acquire.  Called one tile AHEAD of the merge that uses it: the Q buffer is recycled when the tile's last S product
+    // retires, which cannot happen before the previous tile's merge has released the accumulators (o_free, below).
+    auto xdot = [&](int T, int it, bool head_first) {
+      ptx::mbar_wait(&bars->q_full[T & 1], (uint32_t)((T >> 1) & 1));
+      if (head_first) ptx::mbar_wait(&bars->x_full[it & 1], (uint32_t)((it >> 1) & 1));
+      const uint8_t* qrow = smem + kSmemQ + (T & 1) * kQBytes + r * kRowBytes;
+      const uint4* kx = reinterpret_cast<const uint4*>(smem + kSmemX + (it & 1) * 2 * kXBytes);   // K row 576
+      float d4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        float qf[8], kf[8];
+        unpack8(*reinterpret_cast<const uint4*>(qrow + ((c ^ (r & 7)) << 4)), qf);
+        unpack8(kx[c], kf);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) d4[i & 3] = fmaf(qf[i], kf[i], d4[i & 3]);
+      }
+      return (d4[0] + d4[1]) + (d4[2] + d4[3]);
+    };
+    int T = 0;
+    float dot_cur = xdot(0, 0, true);
+    for (int it = 0; it < n_it; ++it) {
+      const int w = head0 + it, f = w / kHeads, h = w % kHeads;
+      const int tb = tile_begin(it), te = tile_end(it);
+      for (int t = tb; t < te; ++t, ++T) {
+        float dot_next = 0.f;
+        if (t + 1 < te) dot_next = xdot(T + 1, it, false);
+        else if (it + 1 < n_it) dot_next = xdot(T + 1, it + 1, true);
+        // One barrier covers everything this merge needs: both groups' (max, sum) of the tile and their last P V products
+        ptx::mbar_wait(&bars->t_done, (uint32_t)(T & 1));
+        const float* x_t = xch + (T & 1) * 256;
+        const float m0 = x_t[r], m1 = x_t[128 + r], l0 = x_t[512 + r], l1 = x_t[512 + 128 + r];
+        const float sx = dot_cur * kLog2e;
+        const float mt = fmaxf(fmaxf(m0, m1), sx);
+        const float f0 = ex2(m0 - mt), f1 = ex2(m1 - mt), px = ex2(sx - mt);
+        const float inv = __fdividef(1.0f, fmaf(l0, f0, l1 * f1) + px);
+        const float c0 = f0 * inv, c1 = f1 * inv, cx = px * inv;
+        const float2 ca2 = make_float2(c0, c0), cb2 = make_float2(c1, c1), cx2 = make_float2(cx, cx), z2 = make_float2(0.f, 0.f);
+        const uint4* vx = reinterpret_cast<const uint4*>(smem + kSmemX + (it & 1) * 2 * kXBytes + kXBytes);   // V row 576
+        if (lane == 0) ptx::bulk_wait_group_read<0>();                   // the previous tile's store has read the slab
+        __syncwarp();
+        ptx::tcgen05_fence_after();
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {                                    // 16 dims at a time
+          uint32_t oa[16], ob[16];
+          ptx::tmem_ld_32x32b_x16(tmem_oa + (uint32_t)(16 * c), oa);
+          ptx::tmem_ld_32x32b_x16(tmem_ob + (uint32_t)(16 * c), ob);
+          ptx::tmem_ld_wait();
+          if (c == 3) {
+            // the accumulators have been read out: the next tile's first P V products may overwrite them
+            ptx::tcgen05_fence_before();
+            ptx::mbar_arrive(&bars->o_free);
+          }
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            float vf[8];
+            unpack8(vx[2 * c + hh], vf);
+            uint32_t wd[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              float2 e = ffma2(make_float2(vf[2 * i], vf[2 * i + 1]), cx2, z2);
+              e = ffma2(make_float2(__uint_as_float(ob[8 * hh + 2 * i]), __uint_as_float(ob[8 * hh + 2 * i + 1])), cb2, e);
+              e = ffma2(make_float2(__uint_as_float(oa[8 * hh + 2 * i]), __uint_as_float(oa[8 * hh + 2 * i + 1])), ca2, e);
+              wd[i] = pack2(e.x, e.y);
+            }
+            // SWIZZLE_128B slab: 16-byte chunk index XOR (row & 7) -- the minimum of four wavefronts per warp store
+            *reinterpret_cast<uint4*>(stage + lane * kRowBytes + (((2 * c + hh) ^ (lane & 7)) << 4)) = make_uint4(wd[0], wd[1], wd[2], wd[3]);
+          }
+        }
+        if (t == te - 1) ptx::mbar_arrive(&bars->x_free[it & 1]);        // the head's rows 576.. are no longer needed
+        ptx::fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_3d(&tmap_out, stage, h * kD, t * kQTile + q * 32, f);   // rows past 577 are clipped by the tensor map
+          ptx::bulk_commit_group();
+        }
+        dot_cur = dot_next;
+      }
+    }
+    if (lane == 0) ptx::bulk_wait_group_read<0>();
   } else {
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 192;");
     // ===== softmax: thread (row r, key group gi) walks its group's key blocks on its own: own running maximum, own
     // row sum, own partial output in TMEM =====
     const int q = warp & 3, gi = warp >> 2;
@@ -346,80 +440,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     const uint32_t tmem_s0 = tmem_base + lane_base + kTmemS + (uint32_t)(gi * 2 * kBlk);
     const uint32_t tmem_o = tmem_base + lane_base + kTmemO + (uint32_t)(gi * kD);
-    const uint32_t tmem_o_other = tmem_base + lane_base + kTmemO + (uint32_t)((gi ^ 1) * kD);
-    float* xch = reinterpret_cast<float*>(smem + kSmemXch);           // [3][2 (tile parity)][2 (group)][128]
+    float* xch = reinterpret_cast<float*>(smem + kSmemXch);           // [2][2 (tile parity)][2 (group)][128]
     constexpr float kLog2e = 1.4426950408889634f;
     float m = -INFINITY, l = 0.f;
-    float dot_cur = 0.f;                                               // this thread's half of q_r . k_576 for the tile
-
-    auto publish = [&](int T) {                                        // at the end of the tile's last block
-      float* x_t = xch + (T & 1) * 256;
-      x_t[gi * 128 + r] = m;
-      x_t[512 + gi * 128 + r] = l;
-      x_t[1024 + gi * 128 + r] = dot_cur;
-      ptx::mbar_arrive(&bars->t_done);
-    };
-    // Merge of local tile T (tile tp of this CTA's it-th head): the two groups' (max, sum, partial output) and the left-over
-    // key 576, whose score is the sum of the two threads' partial dot products.  Each thread finishes 32 of the 64 dims.
-    auto merge = [&](int T, int it, int tp, bool head_done) {
-      const int w = head0 + it, f = w / kHeads, h = w % kHeads;
-      const bool trc = (lane == 0);
-      [[maybe_unused]] const int last = (T % 5) * kNBlk + kNBlk - 1;   // trace slot
-      const float* x_t = xch + (T & 1) * 256;
-      const float m_me = x_t[gi * 128 + r], l_me = x_t[512 + gi * 128 + r];
-      // The partner group runs on its own clock.  One barrier covers everything this merge needs from it and from the
-      // tensor pipe; it cannot run a phase ahead because the next tile's P V products wait for o_free, released below.
-      if (trc) TR(warp * 256 + last * 16 + 10);
-      ptx::mbar_wait(&bars->t_done, (uint32_t)(T & 1));
-      if (trc) TR(warp * 256 + last * 16 + 7);
-      const float mo = x_t[(gi ^ 1) * 128 + r], lo = x_t[512 + (gi ^ 1) * 128 + r];
-      const float sx = (x_t[1024 + gi * 128 + r] + x_t[1024 + (gi ^ 1) * 128 + r]) * kLog2e;
-      ptx::tcgen05_fence_after();
-      uint32_t oa[32], ob[32];
-      ptx::tmem_ld_32x32b_x32(tmem_o + (uint32_t)(gi * 32), oa);
-      ptx::tmem_ld_32x32b_x32(tmem_o_other + (uint32_t)(gi * 32), ob);
-      ptx::tmem_ld_wait();
-      ptx::tcgen05_fence_before();
-      ptx::mbar_arrive(&bars->o_free);
-      if (trc) TR(warp * 256 + last * 16 + 8);
-      const float mt = fmaxf(fmaxf(m_me, mo), sx);
-      const float fa = ex2(m_me - mt), fb = ex2(mo - mt), px = ex2(sx - mt);
-      const float inv = __fdividef(1.0f, fmaf(l_me, fa, lo * fb) + px);
-      const float ca = fa * inv, cb = fb * inv, cx = px * inv;
-      // 32 rows x 32 dims of this warp go out as one TMA store (rows past 577 are clipped by the tensor map)
-      uint8_t* stage = smem + kSmemStage + warp * kStageBytes;
-      if (lane == 0) ptx::bulk_wait_group_read<0>();                   // the previous tile's store has read the slab
-      __syncwarp();
-      const uint4* vx = reinterpret_cast<const uint4*>(smem + kSmemX + (it & 1) * 2 * kXBytes + kXBytes) + gi * 4;   // V row 576
-      const float2 ca2 = make_float2(ca, ca), cb2 = make_float2(cb, cb), cx2 = make_float2(cx, cx), z2 = make_float2(0.f, 0.f);
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        float vf[8];
-        unpack8(vx[c], vf);
-        uint32_t wd[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          float2 e = ffma2(make_float2(vf[2 * i], vf[2 * i + 1]), cx2, z2);
-          e = ffma2(make_float2(__uint_as_float(ob[8 * c + 2 * i]), __uint_as_float(ob[8 * c + 2 * i + 1])), cb2, e);
-          e = ffma2(make_float2(__uint_as_float(oa[8 * c + 2 * i]), __uint_as_float(oa[8 * c + 2 * i + 1])), ca2, e);
-          wd[i] = pack2(e.x, e.y);
-        }
-        *reinterpret_cast<uint4*>(stage + lane * 64 + c * 16) = make_uint4(wd[0], wd[1], wd[2], wd[3]);
-      }
-      if (head_done) ptx::mbar_arrive(&bars->x_free[it & 1]);          // the head's rows 576.. are no longer needed
-      if (trc) TR(warp * 256 + last * 16 + 13);
-      ptx::fence_proxy_async();
-      __syncwarp();
-      if (lane == 0) {
-        tma_store_3d(&tmap_out, stage, h * kD + gi * 32, tp * kQTile + q * 32, f);
-        ptx::bulk_commit_group();
-      }
-      if (trc) TR(warp * 256 + last * 16 + 9);
-    };
 
     int N = 0, T = 0;
-    int m_it = 0, m_tp = 0;                                            // tile T-1, whose merge is still to be done
-    bool m_done = false;
     for (int it = 0; it < n_it; ++it) {
       const bool trc = (lane == 0);
       const int tb = tile_begin(it), te = tile_end(it);
@@ -431,8 +456,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           if (trc) TR(warp * 256 + n * 16 + 0);
           ptx::mbar_wait(&bars->s_full[gi][b], (uint32_t)((N >> 1) & 1));
           if (gi == 1 && t == tb && j == 0) {
-            // Run the two key groups out of phase: while one is in its exp2 stretch (MUFU bound) the other loads, reduces,
-            // merges or waits.  Both groups meet at a head's first S block (they wait for the same K / Q loads), so the
+            // Run the two key groups out of phase: while one is in its exp2 stretch (MUFU bound) the other loads and
+            // reduces.  Both groups meet at a head's first S block (they wait for the same K / Q loads), so the
             // offset is re-established there: group 1 starts this block only when group 0 is two thirds through the exp2
             // of its own first block (an event, not a count of clock cycles).  Group 0 cannot be a head ahead here: every
             // tile's merge needs both groups, so the parity wait is exact.
@@ -444,26 +469,6 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           ptx::tmem_ld_32x32b_x32(ts, v[0]);
           ptx::tmem_ld_32x32b_x32(ts + 32u, v[1]);
           ptx::tmem_ld_32x32b_x32(ts + 64u, v[2]);
-          float dot = 0.f;
-          if (j == 0) {
-            // this thread's half of q_r . k_576, while the TMEM load is in flight.  The Q tile stays put until both
-            // issuers have committed the tile's last S product, which cannot happen before this thread hands over P of
-            // this very block; the waits below are only the acquire on the TMA-written data.
-            ptx::mbar_wait(&bars->q_full[T & 1], (uint32_t)((T >> 1) & 1));
-            if (t == tb) ptx::mbar_wait(&bars->x_full[it & 1], (uint32_t)((it >> 1) & 1));
-            const uint8_t* qrow = smem + kSmemQ + (T & 1) * kQBytes + r * kRowBytes;
-            const uint4* kx = reinterpret_cast<const uint4*>(smem + kSmemX + (it & 1) * 2 * kXBytes) + gi * 4;   // K row 576
-            float d4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-              float qf[8], kf[8];
-              unpack8(*reinterpret_cast<const uint4*>(qrow + (((gi * 4 + c) ^ (r & 7)) << 4)), qf);
-              unpack8(kx[c], kf);
-#pragma unroll
-              for (int i = 0; i < 8; ++i) d4[i & 3] = fmaf(qf[i], kf[i], d4[i & 3]);
-            }
-            dot = (d4[0] + d4[1]) + (d4[2] + d4[3]);
-          }
           ptx::tmem_ld_wait();
           if (trc) TR(warp * 256 + n * 16 + 2);
           float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
@@ -529,26 +534,22 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           ptx::tcgen05_fence_before();
           ptx::mbar_arrive(&bars->p_full[gi][b]);
           if (trc) TR(warp * 256 + n * 16 + 5);
-          if (j == 0) {
-            // With this tile's first block handed to the tensor pipe, finish the previous tile (possibly the previous head's
-            // last one): its last P V has had a whole block's time to retire, so the wait inside returns at once.
-            if (T > 0) merge(T - 1, m_it, m_tp, m_done);
-            m_it = it; m_tp = t; m_done = (t == te - 1);
-            dot_cur = dot;
-          } else if (j == kNBlk - 1) {
-            publish(T);
+          if (j == kNBlk - 1) {
+            // end of the tile: hand (max, sum) to the merge warps and go straight on
+            float* x_t = xch + (T & 1) * 256;
+            x_t[gi * 128 + r] = m;
+            x_t[512 + gi * 128 + r] = l;
+            ptx::mbar_arrive(&bars->t_done);
           }
         }
       }
     }
-    merge(T - 1, m_it, m_tp, m_done);
-    if (lane == 0) ptx::bulk_wait_group_read<0>();
   }
 
   ptx::tcgen05_fence_before();
   __syncthreads();
   ptx::tcgen05_fence_after();
-  if (warp == 10) ptx::tmem_dealloc(tmem_base, kTmemCols);
+  if (warp == 14) ptx::tmem_dealloc(tmem_base, kTmemCols);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -586,14 +587,15 @@ int attention_impl(const void* qkv, int n_frames_total, void* out, cudaStream_t 
     r = fn(&tm_kv, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(qkv), dims, strides, box_kv, estr,
            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  // out viewed as [F][577][1024]: a warp stores 32 rows x 32 dims at a time, rows past 577 are clipped
+  // out viewed as [F][577][1024]: a merge warp stores 32 rows x 64 dims (one head) at a time from a SWIZZLE_128B slab,
+  // rows past 577 are clipped
   CUtensorMap tm_out;
   cuuint64_t odims[3] = {kHeads * kD, (cuuint64_t)kS, (cuuint64_t)n_frames_total};
   cuuint64_t ostrides[2] = {(cuuint64_t)kHeads * kD * 2, (cuuint64_t)kS * kHeads * kD * 2};
-  cuuint32_t box_o[3] = {32, 32, 1};
+  cuuint32_t box_o[3] = {kD, 32, 1};
   if (r == CUDA_SUCCESS)
     r = fn(&tm_out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, out, odims, ostrides, box_o, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_error("attention: cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return EGPT_ERR_CUDA; }
   // per launch: the attribute is per device, and one process may drive several GPUs
   EGPT_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
