@@ -26,7 +26,7 @@
 //   warp 14    TMEM allocator (2 groups x 2 x 96 columns for S / P, 2 x 64 for the partial outputs)
 // The control warps sit in the highest warp ids: the warp arbiter favours them, and the single-thread issuers
 // must not starve for issue slots behind the busy softmax warps.  Registers are handed from the control and merge
-// warps to the softmax warps with setmaxnreg (56 / 72 / 192 per thread).
+// warps to the softmax warps with setmaxnreg (56 / 104 / 176 per thread).
 #include "common.cuh"
 #include "sm100_ptx.cuh"
 
@@ -43,6 +43,12 @@ constexpr int kGroupKeys = 3 * kBlk;                      // 288: key group 0 = 
 constexpr int kXKey = 2 * kGroupKeys;                     // 576: the left-over key, handled outside the MMAs
 constexpr int kNBlk = 3;                                  // blocks per group and tile
 constexpr int kThreads = 512;
+#ifndef EGPT_ATTN_ROLES
+#define EGPT_ATTN_ROLES 0
+#endif
+// control warp ids (12..15): TMA producer, the two MMA issuers, TMEM allocator
+constexpr int kWarpProd = EGPT_ATTN_ROLES == 0 ? 12 : 13, kWarpIss0 = EGPT_ATTN_ROLES == 0 ? 13 : 12;
+constexpr int kWarpIss1 = EGPT_ATTN_ROLES == 0 ? 15 : 14, kWarpAlloc = EGPT_ATTN_ROLES == 0 ? 14 : 15;
 constexpr int kRowBytes = 128;                            // 64 bf16
 constexpr int kKVBytes = kXKey * kRowBytes;               // 73728: 576 keys
 constexpr int kQBytes = kQTile * kRowBytes;               // 16384
@@ -60,6 +66,10 @@ constexpr uint32_t kTmemS = 0, kTmemO = 4 * kBlk;         // columns: S/P [group
 #ifndef EGPT_ATTN_POLY_EVERY
 #define EGPT_ATTN_POLY_EVERY 4
 #endif
+#ifndef EGPT_ATTN_RELEASE_AT
+#define EGPT_ATTN_RELEASE_AT 0
+#endif
+constexpr int kReleaseAt = EGPT_ATTN_RELEASE_AT;          // third of the exp2 stretch after which the partner warp may start its own
 constexpr int kPolyEvery = EGPT_ATTN_POLY_EVERY;          // every kPolyEvery-th pair of exp2 runs as a cubic on the FMA pipe (0: none)
 
 // MN-major B operand (V block: rows = keys (K), 64 contiguous dims (N) = 128 B per key, SWIZZLE_128B):
@@ -157,11 +167,11 @@ struct Bars {
   uint64_t s_full[2][2];                 // [group][buffer]: S block landed
   uint64_t p_full[2][2];                 // [group][buffer]: P stored over it by the group's 128 threads
   uint64_t o_done[2][2];                 // [group][block parity]: P V of a block retired
-  uint64_t o_free;                       // the tile's two partial outputs were read out by the 128 merge threads
-  uint64_t t_done;                       // per tile: both groups' (max, sum) are in shared memory (256 arrivals) and
-                                         // both groups' last P V has retired (2 commits)
-  uint64_t stagger;                      // per head: key group 0 is two thirds through the exp2 of its first block (4 warps)
+  uint64_t o_free[2];                    // [group]: the tile's partial output of that group was read out by the 128 merge threads
+  uint64_t g_done[2];                    // [group], per tile: the group's (max, sum) are in shared memory (128 arrivals) and its
+                                         // last P V has retired (1 commit)
   uint32_t tmem_ptr;
+  float zero;                            // 0.0f, re-read after the turn-taking barrier (see the softmax warps)
 };
 
 // 8 bf16 (one 16-byte chunk of a SWIZZLE_128B row) -> fp32
@@ -203,8 +213,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   auto tile_begin = [&](int it) { return it == 0 ? g0 - head0 * kQTiles : 0; };
   auto tile_end = [&](int it) { return it == n_it - 1 ? g1 - (head0 + it) * kQTiles : kQTiles; };
 
-  if (warp == 12 && lane == 0) { ptx::prefetch_tensormap(&tmap_q); ptx::prefetch_tensormap(&tmap_kv); ptx::prefetch_tensormap(&tmap_out); }
-  if (warp == 13 && lane == 0) {
+  if (warp == kWarpProd && lane == 0) { ptx::prefetch_tensormap(&tmap_q); ptx::prefetch_tensormap(&tmap_kv); ptx::prefetch_tensormap(&tmap_out); }
+  if (warp == kWarpIss0 && lane == 0) {
     for (int g = 0; g < 2; ++g) {
       for (int i = 0; i < kNBlk; ++i) {
         ptx::mbar_init(&bars->k_full[g][i], 1); ptx::mbar_init(&bars->v_full[g][i], 1);
@@ -216,12 +226,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         ptx::mbar_init(&bars->s_full[g][i], 1); ptx::mbar_init(&bars->p_full[g][i], 128); ptx::mbar_init(&bars->o_done[g][i], 1);
       }
     }
-    ptx::mbar_init(&bars->o_free, 128);
-    ptx::mbar_init(&bars->t_done, 258);
-    ptx::mbar_init(&bars->stagger, 4);
+    for (int g = 0; g < 2; ++g) { ptx::mbar_init(&bars->o_free[g], 128); ptx::mbar_init(&bars->g_done[g], 129); }
+    bars->zero = 0.f;
     ptx::fence_barrier_init();
   }
-  if (warp == 14) {
+  if (warp == kWarpAlloc) {
     ptx::tmem_alloc(&bars->tmem_ptr, kTmemCols);
     ptx::tmem_relinquish();
   }
@@ -232,7 +241,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
 
   if (warp >= 12) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
-    if (warp == 12 && lane == 0) {
+    if (warp == kWarpProd && lane == 0) {
       // ===== TMA producer =====
       int T = 0;                                                       // tiles loaded so far
       for (int it = 0; it < n_it; ++it) {
@@ -274,10 +283,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         }
         for (int t = tb + 2; t < te; ++t) load_q(t);
       }
-    } else if (warp == 13 || warp == 15) {
+    } else if (warp == kWarpIss0 || warp == kWarpIss1) {
       // ===== MMA issuer of key group gi: an independent in-order stream of S and P V products.  The whole warp walks the
       // loop (uniform control flow and operands, so descriptors live in uniform registers); one elected lane issues =====
-      const int gi = warp == 13 ? 0 : 1;
+      const int gi = warp == kWarpIss0 ? 0 : 1;
       const uint64_t dK0 = ptx::make_smem_desc_sw128(ptx::smem_u32(smem + kSmemK + gi * kGroupKeys * kRowBytes));
       const uint64_t dV0 = make_desc_mn_sw128(ptx::smem_u32(smem + kSmemV + gi * kGroupKeys * kRowBytes));
       const uint64_t dQ0 = ptx::make_smem_desc_sw128(ptx::smem_u32(smem + kSmemQ));
@@ -293,7 +302,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         ptx::mbar_wait(&bars->p_full[gi][b], (uint32_t)((N >> 1) & 1));
         TR(2048 + gi * 256 + (N % 16) * 8 + 3);
         // the first block of a tile overwrites the accumulator: the previous tile's output must have been read out
-        if (j == 0 && T > 0) ptx::mbar_wait(&bars->o_free, (uint32_t)((T - 1) & 1));
+        if (j == 0 && T > 0) ptx::mbar_wait(&bars->o_free[gi], (uint32_t)((T - 1) & 1));
         ptx::tcgen05_fence_after();
         const uint32_t tmem_p = tmem_s0 + (uint32_t)(b * kBlk);
         // A = P from TMEM: 16 keys = 8 packed columns per k-step; B = V rows 16*kk .. +15 of the block (2048 B = 128 units)
@@ -303,7 +312,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           for (int kk = 0; kk < kBlk / 16; ++kk)
             umma_bf16_ts(tmem_o, tmem_p + (uint32_t)(kk * 8), dv + (uint64_t)(kk * 128), idesc_pv, (j != 0 || kk != 0) ? 1u : 0u);
           ptx::umma_commit(&bars->o_done[gi][b]);
-          if (j == kNBlk - 1) ptx::umma_commit(&bars->t_done);
+          if (j == kNBlk - 1) ptx::umma_commit(&bars->g_done[gi]);
           if (last) ptx::umma_commit(&bars->v_free[gi][j]);                  // the head's last use of this V block
         }
         __syncwarp();
@@ -342,7 +351,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       issue_pv(N - 1, p_it, p_T, p_j, p_first, p_last);
     }
   } else if (warp >= 8) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 104;");
     // ===== merge / output: thread = row r of the tile, all 64 dims.  Runs one tile behind the softmax warps. =====
     const int q = warp & 3;
     const int r = q * 32 + lane;                       // row inside the tile == TMEM lane
@@ -377,12 +386,29 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       const int tb = tile_begin(it), te = tile_end(it);
       for (int t = tb; t < te; ++t, ++T) {
         float dot_next = 0.f;
+        if (q == 0 && lane == 0) TR(3072 + (T % 16) * 8 + 0);
         if (t + 1 < te) dot_next = xdot(T + 1, it, false);
         else if (it + 1 < n_it) dot_next = xdot(T + 1, it + 1, true);
-        // One barrier covers everything this merge needs: both groups' (max, sum) of the tile and their last P V products
-        ptx::mbar_wait(&bars->t_done, (uint32_t)(T & 1));
+        // The two key groups run on their own clocks (group 0 leads by about one block).  Each group's accumulator is read out and
+        // released as soon as THAT group's last P V of the tile has retired, so neither group's next tile waits for the other:
+        // group 0's partial output sits in registers, unscaled, until group 1's maximum is known.
+        if (q == 0 && lane == 0) TR(3072 + (T % 16) * 8 + 1);
         const float* x_t = xch + (T & 1) * 256;
-        const float m0 = x_t[r], m1 = x_t[128 + r], l0 = x_t[512 + r], l1 = x_t[512 + 128 + r];
+        ptx::mbar_wait(&bars->g_done[0], (uint32_t)(T & 1));
+        if (q == 0 && lane == 0) TR(3072 + (T % 16) * 8 + 2);
+        ptx::tcgen05_fence_after();
+        uint32_t oa[4][16];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) ptx::tmem_ld_32x32b_x16(tmem_oa + (uint32_t)(16 * c), oa[c]);
+        const float m0 = x_t[r], l0 = x_t[512 + r];
+        ptx::tmem_ld_wait();
+        ptx::tcgen05_fence_before();
+        ptx::mbar_arrive(&bars->o_free[0]);
+        if (q == 0 && lane == 0) TR(3072 + (T % 16) * 8 + 3);
+        ptx::mbar_wait(&bars->g_done[1], (uint32_t)(T & 1));
+        if (q == 0 && lane == 0) TR(3072 + (T % 16) * 8 + 5);
+        ptx::tcgen05_fence_after();
+        const float m1 = x_t[128 + r], l1 = x_t[512 + 128 + r];
         const float sx = dot_cur * kLog2e;
         const float mt = fmaxf(fmaxf(m0, m1), sx);
         const float f0 = ex2(m0 - mt), f1 = ex2(m1 - mt), px = ex2(sx - mt);
@@ -392,17 +418,15 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         const uint4* vx = reinterpret_cast<const uint4*>(smem + kSmemX + (it & 1) * 2 * kXBytes + kXBytes);   // V row 576
         if (lane == 0) ptx::bulk_wait_group_read<0>();                   // the previous tile's store has read the slab
         __syncwarp();
-        ptx::tcgen05_fence_after();
 #pragma unroll
         for (int c = 0; c < 4; ++c) {                                    // 16 dims at a time
-          uint32_t oa[16], ob[16];
-          ptx::tmem_ld_32x32b_x16(tmem_oa + (uint32_t)(16 * c), oa);
+          uint32_t ob[16];
           ptx::tmem_ld_32x32b_x16(tmem_ob + (uint32_t)(16 * c), ob);
           ptx::tmem_ld_wait();
           if (c == 3) {
-            // the accumulators have been read out: the next tile's first P V products may overwrite them
             ptx::tcgen05_fence_before();
-            ptx::mbar_arrive(&bars->o_free);
+            ptx::mbar_arrive(&bars->o_free[1]);
+            if (q == 0 && lane == 0) TR(3072 + (T % 16) * 8 + 6);
           }
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
@@ -413,7 +437,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             for (int i = 0; i < 4; ++i) {
               float2 e = ffma2(make_float2(vf[2 * i], vf[2 * i + 1]), cx2, z2);
               e = ffma2(make_float2(__uint_as_float(ob[8 * hh + 2 * i]), __uint_as_float(ob[8 * hh + 2 * i + 1])), cb2, e);
-              e = ffma2(make_float2(__uint_as_float(oa[8 * hh + 2 * i]), __uint_as_float(oa[8 * hh + 2 * i + 1])), ca2, e);
+              e = ffma2(make_float2(__uint_as_float(oa[c][8 * hh + 2 * i]), __uint_as_float(oa[c][8 * hh + 2 * i + 1])), ca2, e);
               wd[i] = pack2(e.x, e.y);
             }
             // SWIZZLE_128B slab: 16-byte chunk index XOR (row & 7) -- the minimum of four wavefronts per warp store
@@ -427,12 +451,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           tma_store_3d(&tmap_out, stage, h * kD, t * kQTile + q * 32, f);   // rows past 577 are clipped by the tensor map
           ptx::bulk_commit_group();
         }
+        if (q == 0 && lane == 0) TR(3072 + (T % 16) * 8 + 4);
         dot_cur = dot_next;
       }
     }
     if (lane == 0) ptx::bulk_wait_group_read<0>();
   } else {
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 192;");
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 176;");
     // ===== softmax: thread (row r, key group gi) walks its group's key blocks on its own: own running maximum, own
     // row sum, own partial output in TMEM =====
     const int q = warp & 3, gi = warp >> 2;
@@ -443,6 +468,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     float* xch = reinterpret_cast<float*>(smem + kSmemXch);           // [2][2 (tile parity)][2 (group)][128]
     constexpr float kLog2e = 1.4426950408889634f;
     float m = -INFINITY, l = 0.f;
+    const int n_blocks = (g1 - g0) * kNBlk;                            // blocks this thread will process
+    if (gi == 1) asm volatile("bar.arrive %0, 64;" ::"r"(1 + q) : "memory");   // group 0 takes the first turn
 
     int N = 0, T = 0;
     for (int it = 0; it < n_it; ++it) {
@@ -455,14 +482,6 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           const uint32_t ts = tmem_s0 + (uint32_t)(b * kBlk);
           if (trc) TR(warp * 256 + n * 16 + 0);
           ptx::mbar_wait(&bars->s_full[gi][b], (uint32_t)((N >> 1) & 1));
-          if (gi == 1 && t == tb && j == 0) {
-            // Run the two key groups out of phase: while one is in its exp2 stretch (MUFU bound) the other loads and
-            // reduces.  Both groups meet at a head's first S block (they wait for the same K / Q loads), so the
-            // offset is re-established there: group 1 starts this block only when group 0 is two thirds through the exp2
-            // of its own first block (an event, not a count of clock cycles).  Group 0 cannot be a head ahead here: every
-            // tile's merge needs both groups, so the parity wait is exact.
-            ptx::mbar_wait(&bars->stagger, (uint32_t)(it & 1));
-          }
           ptx::tcgen05_fence_after();
           if (trc) TR(warp * 256 + n * 16 + 1);
           uint32_t v[3][32];
@@ -504,9 +523,18 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             }
           }
           if (trc) TR(warp * 256 + n * 16 + 3);
+          // The exp2 stretch is bound by the scheduler's MUFU unit, which this warp shares with the other key group's warp of
+          // the same TMEM lane quarter (warp ^ 4).  The two take turns: one runs its exp2 stretch at the unit's full rate
+          // while the other waits for S, loads it and finds the row maximum -- instead of both crawling through overlapping
+          // stretches and then idling the unit together.  Two named barriers per warp pair (64 threads: one warp syncs, the
+          // other arrives); group 0 goes first, and both groups have the same number of blocks.
+          asm volatile("bar.sync %0, 64;" ::"r"(1 + gi * 4 + q) : "memory");
+          // ptxas moves register-only math across a barrier (it hoisted 28 of the 72 MUFUs above this one): every exp2 below
+          // takes -m as an input, and -m now depends on a shared-memory load that cannot move above the barrier.
+          const float mz = m + *reinterpret_cast<const volatile float*>(&bars->zero);
           // exp2 on packed fp32x2 instructions (FFMA2 / FADD2): scale, cubic and row sum cost half the issue slots
           float2 s2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
-          const float2 sc = make_float2(kLog2e, kLog2e), nm = make_float2(-m, -m);
+          const float2 sc = make_float2(kLog2e, kLog2e), nm = make_float2(-mz, -mz);
 #pragma unroll
           for (int c = 0; c < 3; ++c) {
             uint32_t wd[16];
@@ -523,10 +551,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
               wd[i] = pack2(pp.x, pp.y);
             }
             tmem_st_32x32b_x16(ts + (uint32_t)(16 * c), wd);          // P over S: column c <- keys 2c, 2c+1
-            if (gi == 0 && c == 1 && t == tb && j == 0) {              // lets group 1 start its first block of this head
-              __syncwarp();
-              if (lane == 0) ptx::mbar_arrive(&bars->stagger);
-            }
+            if (c == kReleaseAt && (gi == 0 || N + 1 < n_blocks))      // the partner warp may start its stretch
+              asm volatile("bar.arrive %0, 64;" ::"r"(1 + (gi ^ 1) * 4 + q) : "memory");
           }
           l += (s2[0].x + s2[0].y) + (s2[1].x + s2[1].y);
           if (trc) TR(warp * 256 + n * 16 + 4);
@@ -539,7 +565,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             float* x_t = xch + (T & 1) * 256;
             x_t[gi * 128 + r] = m;
             x_t[512 + gi * 128 + r] = l;
-            ptx::mbar_arrive(&bars->t_done);
+            ptx::mbar_arrive(&bars->g_done[gi]);
           }
         }
       }
@@ -549,7 +575,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   ptx::tcgen05_fence_before();
   __syncthreads();
   ptx::tcgen05_fence_after();
-  if (warp == 14) ptx::tmem_dealloc(tmem_base, kTmemCols);
+  if (warp == kWarpAlloc) ptx::tmem_dealloc(tmem_base, kTmemCols);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,

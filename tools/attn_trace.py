@@ -22,10 +22,16 @@ def deltas(row):
     return [row[i + 1] - row[i] if row[i + 1] is not None and row[i] is not None else None for i in range(len(row) - 1)]
 names = ["s_full wait", "ld", "max/rescale", "exps+st issue", "st_wait+arrive"]
 for w in (0, 4):
-    print(f"softmax warp {w} (group {w // 4}, rows 0-31) lane 0: block start, deltas {names}, block end, then merge [start, tile done, O loaded + o_free, computed + staged, TMA issued]")
+    print(f"softmax warp {w} (group {w // 4}, rows 0-31) lane 0: block start, deltas {names}, block end")
     for n in range(15):
-        row = [rel(x) for x in t[w * 256 + n * 16: w * 256 + n * 16 + 14]]
-        print(f"  n={n:2d} start {row[0]}  {deltas(row[:6])}  end {row[5]}  merge {[row[k] for k in (10, 7, 8, 13, 9)] if row[7] else ''}")
+        row = [rel(x) for x in t[w * 256 + n * 16: w * 256 + n * 16 + 6]]
+        print(f"  n={n:2d} start {row[0]}  {deltas(row[:6])}  end {row[5]}")
+print("per softmax warp 0..7: [s_full wait, ld, max/rescale, exps+st, arrive] of blocks 3..8")
+for n in range(3, 9):
+    print(f"  n={n:2d}", [[t[w * 256 + n * 16 + k + 1] - t[w * 256 + n * 16 + k] for k in range(5)] for w in range(8)])
+print("block start per softmax warp 0..7:")
+for n in range(15):
+    print(f"  n={n:2d}", [rel(t[w * 256 + n * 16 + 0]) for w in range(8)])
 print("block end (P handed over) per softmax warp 0..7:")
 for n in range(15):
     print(f"  n={n:2d}", [rel(t[w * 256 + n * 16 + 5]) for w in range(8)])
@@ -36,3 +42,7 @@ for g in range(2):
     print(f"issuer {g}: [S issue start, S committed] [pv: p_full wait start, got, committed]")
     for n in range(15):
         print(f"  n={n:2d}", [rel(x) for x in t[2048 + g * 256 + n * 8: 2048 + g * 256 + n * 8 + 5]])
+print("merge warp 8 lane 0, per tile: [start (next tile's left-over dot), wait for group 0, group 0 done, O_0 read + o_free[0], group 1 done, O_1 read + o_free[1], TMA store issued]")
+for n in range(16):
+    row = [rel(t[3072 + n * 8 + k]) for k in (0, 1, 2, 3, 5, 6, 4)]
+    if row[0] is not None: print(f"  T={n:2d}", row)
