@@ -11,13 +11,16 @@
 //              registers, P_n = exp2(S_n - m) goes back over it as packed bf16 (tcgen05.st), the group's partial
 //              output accumulates in TMEM across the three blocks and is rescaled in place only when a block
 //              raises the row maximum by more than 2^8 (otherwise the stale maximum is kept: p <= 256 is harmless
-//              in fp32 / bf16).  A quarter of the exp2 runs as a cubic on the FMA pipe.  The softmax warps do
+//              in fp32 / bf16).  A quarter of the exp2 runs as a cubic on the FMA pipe.  The two warps that share a
+//              scheduler (same lane quarter, different group) take turns on its MUFU unit: a warp starts its exp2 stretch
+//              only when its partner is a third into its own (named barriers, 64 threads each).  The softmax warps do
 //              nothing else: at the end of a tile they publish (max, sum) and go straight on to the next tile.
 //   warps 8-11 merge / output: one thread per row.  The left-over key 576 is handled here on the CUDA cores (a
-//              64-long dot product per row, computed one tile ahead while the Q tile is still resident); when both
-//              groups' last P V of tile t has retired the thread reads the two partial outputs from TMEM, combines
-//              them with the left-over key's term and normalises, and the warp stores its 32 rows x 64 dims with one
-//              TMA store.  This used to run inside the softmax warps and cost them a third of every tile.
+//              64-long dot product per row, computed one tile ahead while the Q tile is still resident).  As soon as
+//              group 0's last P V of tile t has retired the thread reads that partial output into registers and
+//              releases the accumulator; when group 1's has, it combines the two with the left-over key's term,
+//              normalises, and the warp stores its 32 rows x 64 dims with one TMA store.  This used to run inside the
+//              softmax warps and cost them a third of every tile.
 //   warp 12    TMA producer: K and V of a head (576 rows x 64 in blocks of 96, each block re-loaded for the next
 //              head as soon as the current head's last product on it has retired; rows 576..591 -- key 576 and
 //              zero fill from the 3-D tensor map -- in a small double buffer), 128-row Q tiles into a double buffer
@@ -43,12 +46,9 @@ constexpr int kGroupKeys = 3 * kBlk;                      // 288: key group 0 = 
 constexpr int kXKey = 2 * kGroupKeys;                     // 576: the left-over key, handled outside the MMAs
 constexpr int kNBlk = 3;                                  // blocks per group and tile
 constexpr int kThreads = 512;
-#ifndef EGPT_ATTN_ROLES
-#define EGPT_ATTN_ROLES 0
-#endif
-// control warp ids (12..15): TMA producer, the two MMA issuers, TMEM allocator
-constexpr int kWarpProd = EGPT_ATTN_ROLES == 0 ? 12 : 13, kWarpIss0 = EGPT_ATTN_ROLES == 0 ? 13 : 12;
-constexpr int kWarpIss1 = EGPT_ATTN_ROLES == 0 ? 15 : 14, kWarpAlloc = EGPT_ATTN_ROLES == 0 ? 14 : 15;
+// control warp ids: TMA producer, the two MMA issuers, TMEM allocator
+constexpr int kWarpProd = 12, kWarpIss0 = 13;
+constexpr int kWarpIss1 = 15, kWarpAlloc = 14;
 constexpr int kRowBytes = 128;                            // 64 bf16
 constexpr int kKVBytes = kXKey * kRowBytes;               // 73728: 576 keys
 constexpr int kQBytes = kQTile * kRowBytes;               // 16384
