@@ -181,17 +181,20 @@ __device__ __forceinline__ void horizontal_fast(const uint8_t* __restrict__ srow
   const int PW = planar_words(pitch);
   // de-interleave the staged rows: 4 pixels = 12 bytes -> one word of R, G and B each
   const int nq = (w + 3) >> 2;
-  for (int it = threadIdx.x; it < (y1 - y0) * nq; it += blockDim.x) {
-    const int r = it / nq, xq = it - r * nq;
-    const uint32_t off = (uint32_t)((frame_off + (size_t)(y0 + r) * w * 3) & 15) + 12u * (uint32_t)xq;
-    const uint32_t* wp = reinterpret_cast<const uint32_t*>(srows + r * pitch + (off & ~3u));
-    const uint32_t sh8 = (off & 3u) * 8u;
-    const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
-    const uint32_t A = __funnelshift_r(w0, w1, sh8), B = __funnelshift_r(w1, w2, sh8), C = __funnelshift_r(w2, w3, sh8);
-    // A = R0 G0 B0 R1, B = G1 B1 R2 G2, C = B2 R3 G3 B3
-    planar[(0 * kHRows + r) * PW + xq] = __byte_perm(__byte_perm(A, B, 0x0630), C, 0x5210);
-    planar[(1 * kHRows + r) * PW + xq] = __byte_perm(__byte_perm(A, B, 0x0741), C, 0x6210);
-    planar[(2 * kHRows + r) * PW + xq] = __byte_perm(__byte_perm(A, B, 0x0052), C, 0x7410);
+  for (int r = threadIdx.x >> 5; r < y1 - y0; r += 11) {               // a warp per row (352 threads = 11 warps)
+    const uint32_t off0 = (uint32_t)((frame_off + (size_t)(y0 + r) * w * 3) & 15);
+    const uint32_t sh8 = (off0 & 3u) * 8u;
+    const uint32_t* wrow = reinterpret_cast<const uint32_t*>(srows + r * pitch + (off0 & ~3u));
+    uint32_t* pr = planar + r * PW;
+    for (int xq = threadIdx.x & 31; xq < nq; xq += 32) {
+      const uint32_t* wp = wrow + 3 * xq;
+      const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
+      const uint32_t A = __funnelshift_r(w0, w1, sh8), B = __funnelshift_r(w1, w2, sh8), C = __funnelshift_r(w2, w3, sh8);
+      // A = R0 G0 B0 R1, B = G1 B1 R2 G2, C = B2 R3 G3 B3
+      pr[xq] = __byte_perm(__byte_perm(A, B, 0x0630), C, 0x5210);
+      pr[kHRows * PW + xq] = __byte_perm(__byte_perm(A, B, 0x0741), C, 0x6210);
+      pr[2 * kHRows * PW + xq] = __byte_perm(__byte_perm(A, B, 0x0052), C, 0x7410);
+    }
   }
   __syncthreads();
   const int o = threadIdx.x;
@@ -205,22 +208,23 @@ __device__ __forceinline__ void horizontal_fast(const uint8_t* __restrict__ srow
     const uint32_t c = __ldg(reinterpret_cast<const uint32_t*>(pp + 2));
     pk[0] = a.x; pk[1] = a.y; pk[2] = a.z; pk[3] = a.w; pk[4] = b.x; pk[5] = b.y; pk[6] = b.z; pk[7] = b.w; pk[8] = c;
   }
+  const uint32_t* pr = planar + (xmin >> 2);                            // planar row (c * 8 + qd * 4 + r): walked in order
+  uint32_t* dq = dstq + (size_t)(y0 >> 2) * 3 * kCrop + o;              // tmp[y / 4][c][o], byte y % 4
+  const bool second = y0 + 4 < h;
 #pragma unroll
-  for (int qd = 0; qd < kHRows / 4; ++qd) {
-    const int y4 = y0 + 4 * qd;
-    if (y4 >= h) break;
+  for (int c = 0; c < 3; ++c) {
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
+    for (int qd = 0; qd < kHRows / 4; ++qd) {
       uint32_t packed = 0u;
 #pragma unroll
       for (int r = 0; r < 4; ++r) {
-        const uint32_t* pr = planar + (c * kHRows + qd * 4 + r) * PW + (xmin >> 2);
         uint32_t wv[4];
 #pragma unroll
         for (int i = 0; i <= NW; ++i) wv[i] = pr[i];
+        pr += PW;
         packed |= (uint32_t)clip8(tap_sum<NW>(wv, sh8, pk)) << (8 * r);
       }
-      dstq[((size_t)(y4 >> 2) * 3 + c) * kCrop + o] = packed;           // tmp[y / 4][c][o], byte y % 4
+      if (qd == 0 || second) dq[(qd * 3 + c) * kCrop] = packed;
     }
   }
 }
@@ -313,7 +317,7 @@ template <int NW>
 __device__ __forceinline__ void vertical_fast(const uint32_t* __restrict__ srcq, uint32_t* __restrict__ sq, const uint16_t* slut,
                                               int h, int yo0, int f, const int32_t* __restrict__ tab,
                                               uint16_t* __restrict__ out_pix, uint16_t* __restrict__ out_patches) {
-  __shared__ uint32_t sk[8][kPlaneInts];
+  __shared__ __align__(16) uint32_t sk[8][kPlaneInts];
   const int o = threadIdx.x;
   const int q_lo = tab[yo0] >> 2, q_need = (tab[yo0 + 7] >> 2) + NW + 1 - q_lo, q_valid = ((h + 3) >> 2) - q_lo;
   const bool staged = q_need <= kVQuads;
@@ -326,29 +330,50 @@ __device__ __forceinline__ void vertical_fast(const uint32_t* __restrict__ srcq,
   if (o < 8 * kPlaneInts) sk[o / kPlaneInts][o % kPlaneInts] = (uint32_t)tab[kPlaneOff + (yo0 + o / kPlaneInts) * kPlaneInts + o % kPlaneInts];
   __syncthreads();
   if (o >= kCrop) return;
+  // per-thread output addressing: column o of pixel_values, patch column px / offset dx of the im2col rows
+  const int px = o / 14, dx = o - px * 14;
+  uint16_t* ppix = out_pix ? out_pix + (size_t)f * 3 * kCrop * kCrop + o : nullptr;
+  uint16_t* ppat = out_patches ? out_patches + ((size_t)f * 576 + px) * kPatchK + dx : nullptr;
+  const int q_last = ((h + 3) >> 2) - 1;
 #pragma unroll 1
   for (int i8 = 0; i8 < 8; ++i8) {
     const int yo = yo0 + i8, ymin = tab[yo];
     const uint32_t sh8 = (uint32_t)(ymin & 3) * 8u;
     uint32_t pk[9];
-#pragma unroll
-    for (int i = 0; i < 9; ++i) pk[i] = sk[i8][i];
-    uint16_t v[3];
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      uint32_t wv[4];
-      if (staged) {
-        const uint32_t* pc = sq + ((size_t)((ymin >> 2) - q_lo) * 3 + c) * kCrop + o;
-#pragma unroll
-        for (int i = 0; i <= NW; ++i) wv[i] = pc[i * kQuadWords];
-      } else {
-#pragma unroll
-        for (int i = 0; i <= NW; ++i)
-          wv[i] = __ldg(srcq + ((size_t)min((ymin >> 2) + i, ((h + 3) >> 2) - 1) * 3 + c) * kCrop + o);
-      }
-      v[c] = slut[clip8(tap_sum<NW>(wv, sh8, pk)) * 3 + c];
+    {
+      const uint4* s4 = reinterpret_cast<const uint4*>(sk[i8]);
+      const uint4 a = s4[0], b = s4[1];
+      pk[0] = a.x; pk[1] = a.y; pk[2] = a.z; pk[3] = a.w; pk[4] = b.x; pk[5] = b.y; pk[6] = b.z; pk[7] = b.w; pk[8] = sk[i8][8];
     }
-    store_pixel(out_pix, out_patches, f, yo, o, v[0], v[1], v[2]);
+    uint16_t v[3];
+    if (staged) {
+      const uint32_t* pc = sq + ((ymin >> 2) - q_lo) * kQuadWords + o;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        uint32_t wv[4];
+#pragma unroll
+        for (int i = 0; i <= NW; ++i) wv[i] = pc[i * kQuadWords + c * kCrop];
+        v[c] = slut[clip8(tap_sum<NW>(wv, sh8, pk)) * 3 + c];
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        uint32_t wv[4];
+#pragma unroll
+        for (int i = 0; i <= NW; ++i) wv[i] = __ldg(srcq + ((size_t)min((ymin >> 2) + i, q_last) * 3 + c) * kCrop + o);
+        v[c] = slut[clip8(tap_sum<NW>(wv, sh8, pk)) * 3 + c];
+      }
+    }
+    if (ppix) {
+      uint16_t* p = ppix + (size_t)yo * kCrop;
+      p[0] = v[0]; p[(size_t)kCrop * kCrop] = v[1]; p[(size_t)2 * kCrop * kCrop] = v[2];
+    }
+    if (ppat) {
+      // im2col row = patch (py*24+px), column = c*196 + dy*14 + dx  (conv weight [1024,3,14,14] flattened)
+      const int py = yo / 14, dy = yo - py * 14;
+      uint16_t* p = ppat + (size_t)py * 24 * kPatchK + dy * 14;
+      p[0] = v[0]; p[196] = v[1]; p[392] = v[2];
+    }
   }
 }
 
