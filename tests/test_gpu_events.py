@@ -332,11 +332,14 @@ def test_device_clip_bounds_and_ranges_vs_reference_goldens(dev):
     assert int(st.item()) & 2
 
 
-@pytest.mark.parametrize("h,w", [(1100, 2000), (340, 1900), (1500, 400)])
+@pytest.mark.parametrize("h,w", [(1100, 2000), (340, 1900), (1500, 400), (720, 1280), (483, 641), (260, 346), (337, 339), (901, 350)])
 def test_preprocess_arbitrary_images_wide_and_deep_filters(h, w, dev):
     """egpt_preprocess on arbitrary uint8 images (the PNG path) at sizes that leave the common fast paths:
     (1100, 2000): rows too wide for the shared-memory staging AND more than 12 filter taps on both axes (scale 3.3);
     (340, 1900): almost no vertical scaling but a 5.6x horizontal reduction (23 taps); (1500, 400): tall, horizontal up-scale.
+    And sizes that take the byte-parallel fast path (at most 12 taps per axis): (720, 1280) needs three packed words per tap
+    window (9-10 taps); (483, 641) and (337, 339) have widths / heights that are no multiples of four (partial pixel quads, a last
+    row quad with rows past the frame); (260, 346) is an up-scale; (901, 350) is tall with 11 vertical taps.
     Bit-exact against the CPU restatement of Pillow's fixed-point bicubic + the CLIP normalisation."""
     from eventgpt_b200 import events as E
     from oracle import preprocess as opp
@@ -353,6 +356,35 @@ def test_preprocess_arbitrary_images_wide_and_deep_filters(h, w, dev):
     got = px.view(torch.int16).cpu().numpy().view(np.uint16)[0]
     want = opp.pixel_values_bf16_bits(img)
     assert np.array_equal(got, want)
+
+
+def test_preprocess_mixed_canvas_sizes_in_one_call(dev):
+    """One egpt_preprocess call over frames of different data-dependent canvases inside one (720, 1280) capacity: 720x1280 (three
+    packed words per tap window), 480x640 (two), 333x517 (odd sizes, row offsets at every alignment) and an empty frame.  Each
+    frame must equal the oracle run on that frame alone."""
+    from eventgpt_b200 import events as E
+    from oracle import preprocess as opp
+    rng = np.random.default_rng(77)
+    H, W = 720, 1280
+    sizes = [(720, 1280), (480, 640), (333, 517), (0, 0)]
+    stride = H * W * 3
+    frames = torch.zeros((len(sizes), stride), dtype=torch.uint8, device=dev)
+    imgs = []
+    for i, (h, w) in enumerate(sizes):
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        imgs.append(img)
+        if h: frames[i, :h * w * 3] = torch.from_numpy(img.reshape(-1)).to(dev)
+    hw = torch.tensor(sizes, dtype=torch.int32, device=dev)
+    px, patches, st = E.preprocess(frames, hw, H, want_patches=True)
+    E.check_status(st, "preprocess")
+    got = px.view(torch.int16).cpu().numpy().view(np.uint16)
+    pat = patches.view(torch.int16).cpu().numpy().view(np.uint16).reshape(len(sizes), 576, -1)
+    for i, (h, w) in enumerate(sizes[:3]):
+        want = opp.pixel_values_bf16_bits(imgs[i])
+        assert np.array_equal(got[i], want), sizes[i]
+        # im2col rows of the same pixels: patch (py, px), column c*196 + dy*14 + dx
+        cols = want.reshape(3, 24, 14, 24, 14).transpose(1, 3, 0, 2, 4).reshape(576, 588)
+        assert np.array_equal(pat[i][:, :588], cols) and not pat[i][:, 588:].any(), sizes[i]
 
 
 @pytest.mark.parametrize("name", ["dsec_000099", "adv_signed_p"])
