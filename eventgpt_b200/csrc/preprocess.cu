@@ -181,12 +181,13 @@ __device__ __forceinline__ void horizontal_fast(const uint8_t* __restrict__ srow
   const int PW = planar_words(pitch);
   // de-interleave the staged rows: 4 pixels = 12 bytes -> one word of R, G and B each
   const int nq = (w + 3) >> 2;
-  for (int r = threadIdx.x >> 5; r < y1 - y0; r += 11) {               // a warp per row (352 threads = 11 warps)
+  const int r = threadIdx.x / 44;                                      // 44 threads per row
+  if (r < y1 - y0) {
     const uint32_t off0 = (uint32_t)((frame_off + (size_t)(y0 + r) * w * 3) & 15);
     const uint32_t sh8 = (off0 & 3u) * 8u;
     const uint32_t* wrow = reinterpret_cast<const uint32_t*>(srows + r * pitch + (off0 & ~3u));
     uint32_t* pr = planar + r * PW;
-    for (int xq = threadIdx.x & 31; xq < nq; xq += 32) {
+    for (int xq = threadIdx.x - r * 44; xq < nq; xq += 44) {
       const uint32_t* wp = wrow + 3 * xq;
       const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
       const uint32_t A = __funnelshift_r(w0, w1, sh8), B = __funnelshift_r(w1, w2, sh8), C = __funnelshift_r(w2, w3, sh8);
@@ -241,12 +242,21 @@ resample_horizontal_kernel(const uint8_t* __restrict__ frames, size_t frame_stri
   const uint8_t* src = frames + (size_t)f * frame_stride;
   const bool staged = pitch > 0 && 3 * w + 32 <= pitch;
   if (staged) {
-    for (int r = 0; r < y1 - y0; ++r) {
+    // 44 threads per row (8 x 44 = 352); every thread has up to three 16-byte loads in flight before it stores the first, so the
+    // CTA pays one global-memory latency per 132 vectors of a row instead of one per row
+    const int r = threadIdx.x / 44, l44 = threadIdx.x - r * 44;
+    if (r < y1 - y0) {
       const size_t gs = (size_t)(y0 + r) * w * 3, a0 = gs & ~(size_t)15;
       const int nvec = (int)((gs + (size_t)w * 3 - a0 + 15) >> 4);
       const uint4* g = reinterpret_cast<const uint4*>(src + a0);
       uint4* d = reinterpret_cast<uint4*>(srows + r * pitch);
-      for (int i = threadIdx.x; i < nvec; i += blockDim.x) d[i] = __ldg(g + i);
+      for (int i0 = l44; i0 < nvec; i0 += 132) {
+        uint4 v[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) if (i0 + 44 * k < nvec) v[k] = __ldg(g + i0 + 44 * k);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) if (i0 + 44 * k < nvec) d[i0 + 44 * k] = v[k];
+      }
     }
     __syncthreads();
   }
@@ -325,9 +335,18 @@ __device__ __forceinline__ void vertical_fast(const uint32_t* __restrict__ srcq,
     const uint4* g = reinterpret_cast<const uint4*>(srcq + (size_t)q_lo * kQuadWords);
     uint4* d = reinterpret_cast<uint4*>(sq);
     const int nvec = min(q_need, q_valid) * (kQuadWords / 4);
-    for (int i = threadIdx.x; i < nvec; i += blockDim.x) d[i] = __ldg(g + i);
+    for (int i0 = threadIdx.x; i0 < nvec; i0 += 4 * 352) {               // four loads in flight per thread
+      uint4 v[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) if (i0 + 352 * k < nvec) v[k] = __ldg(g + i0 + 352 * k);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) if (i0 + 352 * k < nvec) d[i0 + 352 * k] = v[k];
+    }
   }
-  if (o < 8 * kPlaneInts) sk[o / kPlaneInts][o % kPlaneInts] = (uint32_t)tab[kPlaneOff + (yo0 + o / kPlaneInts) * kPlaneInts + o % kPlaneInts];
+  if (o < 8 * kPlaneInts) {
+    const int i8 = o / kPlaneInts, i = o - i8 * kPlaneInts;              // words 0..8: planes, word 9: the row's first tap
+    sk[i8][i] = i == 9 ? (uint32_t)tab[yo0 + i8] : (uint32_t)tab[kPlaneOff + (yo0 + i8) * kPlaneInts + i];
+  }
   __syncthreads();
   if (o >= kCrop) return;
   // per-thread output addressing: column o of pixel_values, patch column px / offset dx of the im2col rows
@@ -337,14 +356,17 @@ __device__ __forceinline__ void vertical_fast(const uint32_t* __restrict__ srcq,
   const int q_last = ((h + 3) >> 2) - 1;
 #pragma unroll 1
   for (int i8 = 0; i8 < 8; ++i8) {
-    const int yo = yo0 + i8, ymin = tab[yo];
-    const uint32_t sh8 = (uint32_t)(ymin & 3) * 8u;
+    const int yo = yo0 + i8;
     uint32_t pk[9];
+    int ymin;
     {
       const uint4* s4 = reinterpret_cast<const uint4*>(sk[i8]);
       const uint4 a = s4[0], b = s4[1];
-      pk[0] = a.x; pk[1] = a.y; pk[2] = a.z; pk[3] = a.w; pk[4] = b.x; pk[5] = b.y; pk[6] = b.z; pk[7] = b.w; pk[8] = sk[i8][8];
+      const uint2 c2 = *reinterpret_cast<const uint2*>(&sk[i8][8]);
+      pk[0] = a.x; pk[1] = a.y; pk[2] = a.z; pk[3] = a.w; pk[4] = b.x; pk[5] = b.y; pk[6] = b.z; pk[7] = b.w; pk[8] = c2.x;
+      ymin = (int)c2.y;
     }
+    const uint32_t sh8 = (uint32_t)(ymin & 3) * 8u;
     uint16_t v[3];
     if (staged) {
       const uint32_t* pc = sq + ((ymin >> 2) - q_lo) * kQuadWords + o;
