@@ -345,8 +345,8 @@ extern "C" int egpt_feature_adaptor(egpt_handle* h, const uint16_t* in, int64_t 
 extern "C" int egpt_encode_pool(egpt_handle* h, const uint16_t* pixel_values, int n_windows, int n_frames,
                                 uint16_t* out_tokens, void* workspace, size_t workspace_bytes, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  EGPT_CHECK_ARG(h && pixel_values && out_tokens && workspace && n_windows > 0 && n_frames > 0 && n_frames <= 8,
-                 "egpt_encode_pool: bad arguments (n_frames must be 1..8)");
+  EGPT_CHECK_ARG(h && pixel_values && out_tokens && workspace && n_windows > 0 && n_frames > 0,
+                 "egpt_encode_pool: bad arguments");
   EGPT_TRY(check_device(h, "egpt_encode_pool"));
   const int F = n_windows * n_frames;
   EGPT_WS_OR_FAIL(F);
@@ -359,8 +359,8 @@ extern "C" int egpt_encode_pool(egpt_handle* h, const uint16_t* pixel_values, in
 extern "C" int egpt_project_pool(egpt_handle* h, const uint16_t* tower_out, int n_windows, int n_frames,
                                  uint16_t* out_tokens, void* workspace, size_t workspace_bytes, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  EGPT_CHECK_ARG(h && tower_out && out_tokens && workspace && n_windows > 0 && n_frames > 0 && n_frames <= 8,
-                 "egpt_project_pool: bad arguments (n_frames must be 1..8)");
+  EGPT_CHECK_ARG(h && tower_out && out_tokens && workspace && n_windows > 0 && n_frames > 0,
+                 "egpt_project_pool: bad arguments");
   EGPT_CHECK_ARG(((uintptr_t)tower_out & 15) == 0 && ((uintptr_t)out_tokens & 15) == 0, "egpt_project_pool: pointers must be 16-byte aligned");
   EGPT_TRY(check_device(h, "egpt_project_pool"));
   const int F = n_windows * n_frames;
@@ -390,7 +390,7 @@ static int visual_tokens_impl(egpt_handle* h, const void* x, const void* y, cons
                               cudaStream_t st) {
   EGPT_CHECK_ARG(h && x && y && p && windows && out_tokens && out_hw && status && workspace,
                  "egpt_visual_tokens: null pointer argument");
-  EGPT_CHECK_ARG(n_windows > 0 && n_frames > 0 && n_frames <= 8 && H > 0 && W > 0, "egpt_visual_tokens: bad shape");
+  EGPT_CHECK_ARG(n_windows > 0 && n_frames > 0 && H > 0 && W > 0, "egpt_visual_tokens: bad shape");
   EGPT_TRY(check_device(h, "egpt_visual_tokens"));
   if (workspace_bytes < egpt_visual_tokens_workspace_bytes(n_windows, n_frames, H, W)) {
     set_error("egpt_visual_tokens: workspace %zu < %zu bytes", workspace_bytes,

@@ -262,6 +262,43 @@ pool_kernel(const T* __restrict__ feat, int t, int s, int c, int n_temporal, T* 
     }
 }
 
+// Any number of frames (t > 8: the reference takes any n, common/common.py:17-37).  Same grid, same partial-sum layout and the same
+// order of additions as pool_kernel, but nothing is kept per frame in registers: the CTA's slab (32 positions x t frames) is walked
+// twice, once position-major for the spatial means and once frame-major for the temporal partial sums (the second walk hits L2).
+template <typename T>
+__global__ void __launch_bounds__(128)
+pool_any_kernel(const T* __restrict__ feat, int t, int s, int c, int n_temporal, T* __restrict__ out, float* __restrict__ partial) {
+  const int b = blockIdx.z, chunk = blockIdx.y, chunks = gridDim.y;
+  const int col = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (col >= c) return;
+  const int s0 = chunk * kPoolRows, s1 = min(s, s0 + kPoolRows);
+  const float inv_t = 1.0f / (float)t;
+  for (int si = s0; si < s1; ++si) {
+    float sp[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int ti = 0; ti < t; ++ti) {
+      float v[8];
+      Vec8<T>::load(feat + (((size_t)b * t + ti) * s + si) * c + col, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sp[j] += v[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sp[j] *= inv_t;
+    Vec8<T>::store(out + ((size_t)b * (n_temporal + s) + n_temporal + si) * c + col, sp);
+  }
+  for (int ti = 0; ti < t; ++ti) {
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int si = s0; si < s1; ++si) {
+      float v[8];
+      Vec8<T>::load(feat + (((size_t)b * t + ti) * s + si) * c + col, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += v[j];
+    }
+    float* p = partial + (((size_t)b * chunks + chunk) * t + ti) * c + col;
+    reinterpret_cast<float4*>(p)[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    reinterpret_cast<float4*>(p)[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+  }
+}
+
 template <typename T>
 __global__ void pool_finish_kernel(const float* __restrict__ partial, int chunks, int t, int s, int c, int n_temporal,
                                    T* __restrict__ out, long long total) {
@@ -405,7 +442,6 @@ extern "C" int egpt_spatio_temporal_pool(const void* features, int is_f32, int b
   EGPT_CHECK_ARG(features && out && workspace, "egpt_spatio_temporal_pool: null pointer argument");
   EGPT_CHECK_ARG(batch > 0 && t > 0 && s > 0 && c > 0 && n_temporal >= 0, "egpt_spatio_temporal_pool: bad shape");
   EGPT_CHECK_ARG(c % 8 == 0, "egpt_spatio_temporal_pool: c=%d must be a multiple of 8", c);
-  if (t > kPoolMaxT) { set_error("egpt_spatio_temporal_pool: t=%d frames > %d supported", t, kPoolMaxT); return EGPT_ERR_UNSUPPORTED; }
   const int chunks = pool_chunks(s);
   const size_t need = (size_t)batch * chunks * t * c * sizeof(float);
   if (workspace_bytes < need) { set_error("egpt_spatio_temporal_pool: workspace %zu < %zu", workspace_bytes, need); return EGPT_ERR_WORKSPACE; }
@@ -416,6 +452,7 @@ extern "C" int egpt_spatio_temporal_pool(const void* features, int is_f32, int b
   const long long total = (long long)batch * n_temporal * c;
   if (is_f32) {
     if (t <= 5) pool_kernel<float, 5><<<grid, 128, 0, st>>>((const float*)features, t, s, c, n_temporal, (float*)out, partial);
+    else if (t > kPoolMaxT) pool_any_kernel<float><<<grid, 128, 0, st>>>((const float*)features, t, s, c, n_temporal, (float*)out, partial);
     else pool_kernel<float, kPoolMaxT><<<grid, 128, 0, st>>>((const float*)features, t, s, c, n_temporal, (float*)out, partial);
     EGPT_LAUNCH_CHECK();
     if (total > 0) {
@@ -424,6 +461,7 @@ extern "C" int egpt_spatio_temporal_pool(const void* features, int is_f32, int b
     }
   } else {
     if (t <= 5) pool_kernel<__nv_bfloat16, 5><<<grid, 128, 0, st>>>((const __nv_bfloat16*)features, t, s, c, n_temporal, (__nv_bfloat16*)out, partial);
+    else if (t > kPoolMaxT) pool_any_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>((const __nv_bfloat16*)features, t, s, c, n_temporal, (__nv_bfloat16*)out, partial);
     else pool_kernel<__nv_bfloat16, kPoolMaxT><<<grid, 128, 0, st>>>((const __nv_bfloat16*)features, t, s, c, n_temporal, (__nv_bfloat16*)out, partial);
     EGPT_LAUNCH_CHECK();
     if (total > 0) {

@@ -238,8 +238,9 @@ int egpt_encode_pool(egpt_handle* h, const uint16_t* pixel_values, int n_windows
 /* a-6 (second half) .. a-8 on cached tower outputs              model/EventChatModel.py:199, 335-342 */
 /* tower_out bf16 [B*n,577,1024] (what egpt_tower returned) -> tokens bf16 [B, n+577, 4096]:       */
 /* visual_projector, feature_adaptor and the pooling without running the tower again; same op      */
-/* order as egpt_encode_pool (pooled before the second projector linear).  n_frames <= 8, like     */
-/* egpt_encode_pool and egpt_visual_tokens (the reference's callers use 5; :119 of common.py).     */
+/* order as egpt_encode_pool (pooled before the second projector linear).  Any n_frames >= 1, like */
+/* egpt_encode_pool and egpt_visual_tokens (the reference's callers use 5, common.py:119; up to 8   */
+/* frames the pooling keeps a frame per register set, beyond that it walks the features twice).     */
 int egpt_project_pool(egpt_handle* h, const uint16_t* tower_out, int n_windows, int n_frames,
                       uint16_t* out_tokens, void* workspace, size_t workspace_bytes, void* stream);
 

@@ -119,6 +119,12 @@ def test_get_spatio_temporal_features(dtype, dev):
         ref = ovit.get_spatio_temporal_features(f.float(), nt)
         assert got.dtype == dtype and tuple(got.shape) == tuple(ref.shape)
         assert (got.float().cpu() - ref).abs().max().item() < tol
+    many = torch.randn(13, 577, 256, generator=g).to(dtype)             # more than 8 frames: the two-walk kernel
+    for nt in (None, 20, 4):
+        got = get_spatio_temporal_features(many.to(dev), nt)
+        ref = ovit.get_spatio_temporal_features(many.float(), nt)
+        assert got.dtype == dtype and tuple(got.shape) == tuple(ref.shape)
+        assert (got.float().cpu() - ref).abs().max().item() < tol
     small = torch.randn(3, 10, 64, generator=g).to(dev)
     ref = ovit.get_spatio_temporal_features(small.cpu())
     assert (get_spatio_temporal_features(small).cpu() - ref).abs().max().item() < 1e-5
@@ -497,10 +503,10 @@ def test_config5_events_to_inputs_embeds(frontends, dev):
     assert torch.equal(emb[0, :5].cpu(), table[ids[0, :5]]) and torch.equal(emb[0, 5:5 + 582], tok[0])
 
 
-@pytest.mark.parametrize("n", [1, 3, 8])
+@pytest.mark.parametrize("n", [1, 3, 8, 11])
 def test_other_frame_counts(n, frontends, dev):
     """get_event_images_list(event_npy, n) takes any n (common/common.py:17-37; the inference caller passes 5): raster,
-    preprocessing and the fused token path for 1, 3 and 8 frames per window -> tokens [B, n + 577, 4096]."""
+    preprocessing and the fused token path for 1, 3, 8 and 11 frames per window -> tokens [B, n + 577, 4096]."""
     from eventgpt_b200 import events as E
     from oracle import events as oev, preprocess as opp
     sd, fe = frontends(2)
