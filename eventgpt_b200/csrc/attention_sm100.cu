@@ -531,7 +531,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           asm volatile("bar.sync %0, 64;" ::"r"(1 + gi * 4 + q) : "memory");
           // ptxas moves register-only math across a barrier (it hoisted 28 of the 72 MUFUs above this one): every exp2 below
           // takes -m as an input, and -m now depends on a shared-memory load that cannot move above the barrier.
-          const float mz = m + *reinterpret_cast<const volatile float*>(&bars->zero);
+          float zero;
+          asm volatile("ld.shared.f32 %0, [%1];" : "=f"(zero) : "r"(ptx::smem_u32(&bars->zero)) : "memory");
+          const float mz = m + zero;
           // exp2 on packed fp32x2 instructions (FFMA2 / FADD2): scale, cubic and row sum cost half the issue slots
           float2 s2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
           const float2 sc = make_float2(kLog2e, kLog2e), nm = make_float2(-mz, -mz);
